@@ -1,0 +1,92 @@
+// AWQ INT4 W4A16 linear: python/sglang/srt/layers/quantization/awq.py:186-204
+//   out = x @ awq_dequantize(qweight, scales, qzeros) (+ bias)
+// v1 keeps the reference's two-phase structure but entirely in our own sm_100a kernels and in the
+// layout the tcgen05 GEMM wants: the weight is dequantised TRANSPOSED into a K-major [N, K] half
+// buffer in the caller's workspace (so both GEMM operands are K-major / SWIZZLE_128B TMA tiles),
+// then gemm_tc_kernel<MODE 2> (tcgen05.mma kind::f16, fp32 accumulate in TMEM) does x . W^T.
+// The dequantised values are bit-identical to awq_dequantize (awq_kernel.cu:126-221).
+#include "common.cuh"
+
+namespace b200 {
+
+int dense_half_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, const void* bias, void* out, int64_t ldo,
+                    int dtype, int M, int N, int K, void* workspace, size_t workspace_bytes, cudaStream_t st);
+size_t dense_half_gemm_workspace(int M, int N, int K);
+
+// block = (32, 8): tile of 64 K-rows x 32 packed columns (= 256 N); out_t[n, k]
+template <bool BF16>
+__global__ void __launch_bounds__(256) awq_dequant_t_kernel(const int32_t* __restrict__ qw,
+                                                            const uint16_t* __restrict__ sc,
+                                                            const int32_t* __restrict__ qz, uint16_t* __restrict__ out_t,
+                                                            int K, int cols, int group) {
+  __shared__ uint16_t tile[256][64 + 8];  // [n_local][k_local], +8 halves padding
+  const int c0 = blockIdx.x * 32, k0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = c0 + tx;
+  for (int kk = ty; kk < 64; kk += 8) {
+    const int k = k0 + kk;
+    if (k < K && c < cols) {
+      const int gi = k / group;
+      const uint32_t w = (uint32_t)qw[(int64_t)k * cols + c], z = (uint32_t)qz[(int64_t)gi * cols + c];
+      const uint4 sraw = *reinterpret_cast<const uint4*>(sc + ((int64_t)gi * cols + c) * 8);
+      const uint32_t sw[4] = {sraw.x, sraw.y, sraw.z, sraw.w};
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int d0 = (int)((w >> (4 * p)) & 15u) - (int)((z >> (4 * p)) & 15u);
+        const int d1 = (int)((w >> (4 * p + 16)) & 15u) - (int)((z >> (4 * p + 16)) & 15u);
+        const float2 s2 = unpack_half2<BF16>(sw[p]);
+        tile[tx * 8 + 2 * p][kk] = float_to_half<BF16>(__fmul_rn((float)d0, s2.x));
+        tile[tx * 8 + 2 * p + 1][kk] = float_to_half<BF16>(__fmul_rn((float)d1, s2.y));
+      }
+    }
+  }
+  __syncthreads();
+  // write 256 rows (n) x 64 k: each thread writes 8 halves (16 B) at a time
+  for (int e = threadIdx.x; e < 256 * 8; e += 256) {
+    const int nl = e >> 3, kc = (e & 7) * 8;
+    const int n = c0 * 8 + nl, k = k0 + kc;
+    if (n < cols * 8 && k < K) {
+      const uint4 v = *reinterpret_cast<const uint4*>(&tile[nl][kc]);
+      *reinterpret_cast<uint4*>(out_t + (int64_t)n * K + k) = v;
+    }
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qweight, const void* scales,
+                                 const int32_t* qzeros, const void* bias, void* out, int64_t ldo, int dtype, int M, int N,
+                                 int K, int group, void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(x && qweight && scales && qzeros && out, B200_ERR_ARG, "awq_w4a16_mm: null tensor");
+  B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, B200_ERR_UNSUPPORTED, "awq_w4a16_mm: activations must be f16/bf16");
+  B200_REQUIRE(M >= 0 && N > 0 && K > 0 && N % 8 == 0 && K % 8 == 0 && group > 0 && K % group == 0, B200_ERR_ARG,
+               "awq_w4a16_mm: need N %% 8 == 0, K %% 8 == 0, K %% group == 0 (N=%d K=%d group=%d)", N, K, group);
+  if (M == 0) return B200_OK;
+  const int arch = b200_sm_arch();
+  B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "awq_w4a16_mm: requires an sm_100 device (got sm_%d); no fallback", arch);
+  const size_t wt_bytes = ((size_t)N * K * 2 + 255) & ~(size_t)255;
+  const size_t gemm_ws = (dense_half_gemm_workspace(M, N, K) + 255) & ~(size_t)255;
+  B200_REQUIRE(workspace && workspace_bytes >= wt_bytes + gemm_ws && ((uintptr_t)workspace & 255) == 0, B200_ERR_ARG,
+               "awq_w4a16_mm: workspace too small or not 256-byte aligned (need %zu bytes, have %zu)", wt_bytes + gemm_ws,
+               workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  // the split-K ticket counters live at the START of the workspace (zeroed once by the caller)
+  uint8_t* gemm_ws_ptr = reinterpret_cast<uint8_t*>(workspace);
+  uint16_t* wt = reinterpret_cast<uint16_t*>(gemm_ws_ptr + gemm_ws);
+  const int cols = N / 8;
+  dim3 grid((cols + 31) / 32, (K + 63) / 64);
+  if (dtype == B200_BF16)
+    awq_dequant_t_kernel<true><<<grid, 256, 0, st>>>(qweight, (const uint16_t*)scales, qzeros, wt, K, cols, group);
+  else
+    awq_dequant_t_kernel<false><<<grid, 256, 0, st>>>(qweight, (const uint16_t*)scales, qzeros, wt, K, cols, group);
+  if (int rc = check_cuda(cudaGetLastError(), "awq_dequant_t_kernel launch")) return rc;
+  return dense_half_gemm(x, ldx, wt, K, bias, out, ldo, dtype, M, N, K, gemm_ws_ptr, gemm_ws, st);
+}
+
+extern "C" size_t b200_awq_w4a16_workspace_size(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return 256;
+  const size_t wt_bytes = ((size_t)N * K * 2 + 255) & ~(size_t)255;
+  return ((dense_half_gemm_workspace(M, N, K) + 255) & ~(size_t)255) + wt_bytes;
+}

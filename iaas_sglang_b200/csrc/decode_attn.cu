@@ -1,0 +1,678 @@
+// Paged-KV decode attention for sm_100a.
+//
+// Replaces (see include/b200_sgl.h): decode_attention_cpu (sgl-kernel/csrc/cpu/decode.cpp:1375-1575),
+// decode_attention_fwd (python/sglang/srt/layers/attention/triton_ops/decode_attention.py:677-728) and the
+// fused KVCache.set_kv_buffer (python/sglang/srt/mem_cache/memory_pool.py:418-456).
+//
+// Design (DESIGN.md "decode attention"): the op is HBM-bound (G..2G flop per KV byte), so the kernel is
+// built around keeping ~200 KB of scattered KV rows in flight per SM:
+//   * grid = (kv split, kv-head group x q-block, request); one CTA per SM (smem-limited);
+//   * a producer warp reads the page table IN PLACE (req_to_token row of the request; no flattened
+//     kv_indices copy) and issues one TMA bulk copy (cp.async.bulk, UBLKCP) per token row per K/V into
+//     a 3..6-stage shared-memory ring; completion is tracked by mbarrier transaction counts;
+//   * 8 consumer warps read the rows with ldmatrix (16-byte vectors), run QK^T and PV on the warp
+//     tensor-core path (mma.sync m16n8k16, fp32 accumulate) with the GQA group padded to the 16-row
+//     MMA tile, and keep an online softmax in registers (quad shuffles for the row max / sum);
+//   * per-warp states are merged through shared memory, per-split states through a small fp32
+//     workspace and an LSE-merge kernel (decode.cpp:812-860 / decode_attention.py:492-552).
+// A generic SIMT kernel covers every other head dimension (incl. MLA 576/512) so that the op has no
+// unsupported shapes and no CPU fallback.
+#include <math.h>
+#include <stdio.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kConsumerWarps = 8;
+constexpr int kAttnThreads = (kConsumerWarps + 1) * 32;
+constexpr int kTokPerWarp = 16;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct DecodeKParams {
+  const uint16_t* q;
+  int64_t q_sb, q_sh;
+  const uint16_t* k_new;
+  int64_t kn_sb, kn_sh;
+  const uint16_t* v_new;
+  int64_t vn_sb, vn_sh;
+  uint16_t* k_buf;
+  int64_t kb_st, kb_sh;
+  uint16_t* v_buf;
+  int64_t vb_st, vb_sh;
+  uint16_t* out;
+  float* part_o;    // [B, Hq, S, Dv]
+  float* part_lse;  // [B, Hq, S]   (log2 domain)
+  const void* r2t;
+  int64_t r2t_stride;
+  const int64_t* rpi;
+  const int64_t* seq_lens;
+  const int64_t* loc;
+  int idx64;
+  int B, Hq, Hkv, G, D, Dv;
+  int num_splits;
+  int fused_new;  // substitute k_new/v_new for the slot out_cache_loc[b] and write it back in-kernel
+  int is_mla;
+  float sm_scale, logit_cap;
+};
+
+template <int D, int HPC>
+struct AttnCfg {
+  static constexpr int WT = kConsumerWarps / HPC;
+  static constexpr int TILE_T = WT * kTokPerWarp;
+  static constexpr int ROW_BYTES = HPC * D * 2;
+  static constexpr int ROW_PITCH = ROW_BYTES + 16;
+  static constexpr int KV_BYTES = TILE_T * ROW_PITCH;
+  static constexpr int STAGE_BYTES = 2 * KV_BYTES;
+  static constexpr int STAGES = (D >= 128) ? 3 : 6;
+  static constexpr int SCRATCH_BYTES = kConsumerWarps * 16 * (D + 2) * 4;
+  static constexpr int RING_BYTES = STAGES * STAGE_BYTES;
+  static constexpr int SMEM_BYTES = (RING_BYTES > SCRATCH_BYTES ? RING_BYTES : SCRATCH_BYTES) + 2 * STAGES * 8 + 16;
+};
+
+__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory"); }
+
+template <int D, int HPC, bool BF16>
+__global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const __grid_constant__ DecodeKParams p) {
+  using C = AttnCfg<D, HPC>;
+  constexpr int Dv = D;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (C::RING_BYTES > C::SCRATCH_BYTES ? C::RING_BYTES : C::SCRATCH_BYTES));
+  uint64_t* empty = full + C::STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.x, b = blockIdx.z;
+  const int n_qblk = (p.G + 15) >> 4;
+  const int hg = blockIdx.y / n_qblk, qblk = blockIdx.y - hg * n_qblk;
+  const int kvh0 = hg * HPC;
+  const int64_t len = p.seq_lens[b];
+  const int64_t req = p.rpi[b];
+  const int64_t loc_b = p.fused_new ? p.loc[b] : -1;
+
+  // tile-aligned split of [0, len)
+  const int64_t per_raw = (len + p.num_splits - 1) / p.num_splits;
+  const int64_t per = (per_raw + C::TILE_T - 1) / C::TILE_T * C::TILE_T;
+  const int64_t kv0 = (int64_t)split * per;
+  const int64_t kv1 = (kv0 + per < len) ? kv0 + per : len;
+  const int n_tiles = kv1 > kv0 ? (int)((kv1 - kv0 + C::TILE_T - 1) / C::TILE_T) : 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kConsumerWarps);
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    // ================================ producer warp ================================
+    if (p.fused_new && split == 0 && qblk == 0) {
+      // fused KVCache.set_kv_buffer for this CTA's heads (memory_pool.py:418-456)
+      const uint4* ks = reinterpret_cast<const uint4*>(p.k_new + b * p.kn_sb + kvh0 * p.kn_sh);
+      const uint4* vs = reinterpret_cast<const uint4*>(p.v_new + b * p.vn_sb + kvh0 * p.vn_sh);
+      uint4* kd = reinterpret_cast<uint4*>(p.k_buf + loc_b * p.kb_st + kvh0 * p.kb_sh);
+      uint4* vd = reinterpret_cast<uint4*>(p.v_buf + loc_b * p.vb_st + kvh0 * p.vb_sh);
+      for (int i = lane; i < C::ROW_BYTES / 16; i += 32) {
+        kd[i] = ks[i];
+        vd[i] = vs[i];
+      }
+    }
+    constexpr int R = (C::TILE_T + 31) / 32;
+    for (int it = 0; it < n_tiles; ++it) {
+      const int s = it % C::STAGES;
+      const uint32_t ph = (it / C::STAGES) & 1;
+      int64_t idx[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int j = lane + 32 * r;
+        int64_t pos = kv0 + (int64_t)it * C::TILE_T + j;
+        if (pos > kv1 - 1) pos = kv1 - 1;  // tail: duplicate the last valid row (masked by the consumers)
+        idx[r] = (j < C::TILE_T) ? load_index(p.r2t, req * p.r2t_stride + pos, p.idx64) : 0;
+      }
+      mbar_wait(&empty[s], ph ^ 1);
+      if (lane == 0) mbar_arrive_expect_tx(&full[s], 2 * C::TILE_T * C::ROW_BYTES);
+      __syncwarp();
+      uint8_t* kdst = smem + s * C::STAGE_BYTES;
+      uint8_t* vdst = kdst + C::KV_BYTES;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int j = lane + 32 * r;
+        if (j < C::TILE_T) {
+          const uint16_t* ksrc = p.k_buf + idx[r] * p.kb_st + kvh0 * p.kb_sh;
+          const uint16_t* vsrc = p.v_buf + idx[r] * p.vb_st + kvh0 * p.vb_sh;
+          if (idx[r] == loc_b) {
+            ksrc = p.k_new + b * p.kn_sb + kvh0 * p.kn_sh;
+            vsrc = p.v_new + b * p.vn_sb + kvh0 * p.vn_sh;
+          }
+          bulk_g2s(kdst + j * C::ROW_PITCH, ksrc, C::ROW_BYTES, &full[s]);
+          bulk_g2s(vdst + j * C::ROW_PITCH, vsrc, C::ROW_BYTES, &full[s]);
+        }
+      }
+    }
+    return;
+  }
+
+  // ================================ consumer warps ================================
+  const int wh = warp / C::WT, wt = warp - wh * C::WT;
+  const int kvh = kvh0 + wh;
+  const int row0 = qblk * 16;                         // first row of the GQA group handled here
+  const int rows_valid = min(16, p.G - row0);
+  const int qh0 = kvh * p.G + row0;
+  const int g = lane >> 2, t = lane & 3;
+
+  if (n_tiles == 0) {
+    // empty split: lse = -inf so that the merge ignores it (cf. decode.cpp:986 writes nothing)
+    if (wt == 0) {
+      if (p.num_splits > 1) {
+        for (int r = lane; r < rows_valid; r += 32)
+          p.part_lse[((int64_t)b * p.Hq + qh0 + r) * p.num_splits + split] = -INFINITY;
+      } else {  // seq_len == 0: defined output (zeros)
+        for (int e = lane; e < rows_valid * Dv; e += 32) p.out[((int64_t)b * p.Hq + qh0) * Dv + e] = 0;
+      }
+    }
+    return;
+  }
+
+  uint32_t qf[D / 16][4];
+  {
+    const uint16_t* q0 = p.q + b * p.q_sb + (int64_t)(qh0 + g) * p.q_sh + 2 * t;
+    const uint16_t* q1 = q0 + 8 * p.q_sh;
+    const bool v0 = g < rows_valid, v1 = g + 8 < rows_valid;
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+      qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16) : 0u;
+      qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16) : 0u;
+      qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 8) : 0u;
+      qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 8) : 0u;
+    }
+  }
+  float o[Dv / 8][4];
+#pragma unroll
+  for (int j = 0; j < Dv / 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+
+  const bool has_cap = p.logit_cap > 0.f;
+  const float scale2 = p.sm_scale * kLog2e;
+  const int lm = lane >> 3, lr = lane & 7;
+  // ldmatrix lane addressing: K non-transposed, V transposed
+  const uint32_t k_lane_off = (uint32_t)(((lm >> 1) * 8 + lr) * C::ROW_PITCH + (lm & 1) * 16);
+  const uint32_t v_lane_off = (uint32_t)(((lm & 1) * 8 + lr) * C::ROW_PITCH + (lm >> 1) * 16);
+  const uint32_t smem_base = smem_u32(smem);
+
+  for (int it = 0; it < n_tiles; ++it) {
+    const int s = it % C::STAGES;
+    const uint32_t ph = (it / C::STAGES) & 1;
+    mbar_wait(&full[s], ph);
+    const uint32_t kbase = smem_base + s * C::STAGE_BYTES + (wt * kTokPerWarp) * C::ROW_PITCH + wh * D * 2;
+    const uint32_t vbase = kbase + C::KV_BYTES;
+
+    float sc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+      uint32_t r0, r1, r2, r3;
+      ldsm_x4(kbase + k_lane_off + ks * 32, r0, r1, r2, r3);
+      mma_16816<BF16>(sc[0], qf[ks], r0, r1);
+      mma_16816<BF16>(sc[1], qf[ks], r2, r3);
+    }
+    const int64_t tok0 = kv0 + (int64_t)it * C::TILE_T + wt * kTokPerWarp;
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = sc[nt][e];
+        if (has_cap) {
+          v *= p.sm_scale;
+          v = p.logit_cap * tanhf(v / p.logit_cap) * kLog2e;
+        } else {
+          v *= scale2;
+        }
+        const int64_t pos = tok0 + nt * 8 + 2 * t + (e & 1);
+        if (pos >= kv1) v = -INFINITY;
+        sc[nt][e] = v;
+        mx[e >> 1] = fmaxf(mx[e >> 1], v);
+      }
+    float alpha[2], m_use[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+      const float m_new = fmaxf(m_run[r], mx[r]);
+      m_use[r] = (m_new == -INFINITY) ? 0.f : m_new;
+      alpha[r] = exp2f(m_run[r] - m_use[r]);
+      m_run[r] = m_new;
+    }
+    uint32_t pa[4];
+    float ps[2] = {0.f, 0.f};
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      const float p0 = exp2f(sc[nt][0] - m_use[0]), p1 = exp2f(sc[nt][1] - m_use[0]);
+      const float p2 = exp2f(sc[nt][2] - m_use[1]), p3 = exp2f(sc[nt][3] - m_use[1]);
+      pa[nt * 2 + 0] = pack_half2<BF16>(p0, p1);
+      pa[nt * 2 + 1] = pack_half2<BF16>(p2, p3);
+      // sum the ROUNDED probabilities so numerator and denominator use the same weights
+      const float2 f01 = unpack_half2<BF16>(pa[nt * 2 + 0]), f23 = unpack_half2<BF16>(pa[nt * 2 + 1]);
+      ps[0] += f01.x + f01.y;
+      ps[1] += f23.x + f23.y;
+    }
+    l_run[0] = l_run[0] * alpha[0] + ps[0];
+    l_run[1] = l_run[1] * alpha[1] + ps[1];
+    if (alpha[0] != 1.f || alpha[1] != 1.f) {
+#pragma unroll
+      for (int j = 0; j < Dv / 8; ++j) {
+        o[j][0] *= alpha[0];
+        o[j][1] *= alpha[0];
+        o[j][2] *= alpha[1];
+        o[j][3] *= alpha[1];
+      }
+    }
+#pragma unroll
+    for (int jp = 0; jp < Dv / 16; ++jp) {
+      uint32_t r0, r1, r2, r3;
+      ldsm_x4_t(vbase + v_lane_off + jp * 32, r0, r1, r2, r3);
+      mma_16816<BF16>(o[2 * jp], pa, r0, r1);
+      mma_16816<BF16>(o[2 * jp + 1], pa, r2, r3);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+  }
+
+  // quad-reduce the row sums
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+
+  // ---- merge the WT token-warps of each head through shared memory (ring is idle now) ----
+  consumer_bar();
+  float* scratch = reinterpret_cast<float*>(smem);  // [warp][16][Dv + 2]
+  {
+    float* my = scratch + (size_t)warp * 16 * (Dv + 2);
+#pragma unroll
+    for (int j = 0; j < Dv / 8; ++j) {
+      *reinterpret_cast<float2*>(my + g * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
+      *reinterpret_cast<float2*>(my + (g + 8) * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][2], o[j][3]);
+    }
+    if (t == 0) {
+      my[g * (Dv + 2) + Dv] = m_run[0];
+      my[g * (Dv + 2) + Dv + 1] = l_run[0];
+      my[(g + 8) * (Dv + 2) + Dv] = m_run[1];
+      my[(g + 8) * (Dv + 2) + Dv + 1] = l_run[1];
+    }
+  }
+  consumer_bar();
+  // every consumer thread produces elements of (head wh', row r, dv): HPC*rows_valid*Dv elements
+  const int tid = threadIdx.x;  // < 256
+  const int total = HPC * rows_valid * Dv;
+  for (int e = tid; e < total; e += kConsumerWarps * 32) {
+    const int dv = e % Dv;
+    const int r = (e / Dv) % rows_valid;
+    const int h = e / (Dv * rows_valid);
+    const float* base = scratch + (size_t)(h * C::WT) * 16 * (Dv + 2) + r * (Dv + 2);
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < C::WT; ++w) M = fmaxf(M, base[(size_t)w * 16 * (Dv + 2) + Dv]);
+    float L = 0.f, O = 0.f;
+    const float Mu = (M == -INFINITY) ? 0.f : M;
+#pragma unroll
+    for (int w = 0; w < C::WT; ++w) {
+      const float* bw = base + (size_t)w * 16 * (Dv + 2);
+      const float sc_w = exp2f(bw[Dv] - Mu);
+      L += bw[Dv + 1] * sc_w;
+      O += bw[dv] * sc_w;
+    }
+    const int head = (kvh0 + h) * p.G + row0 + r;
+    const float inv = L > 0.f ? 1.f / L : 0.f;
+    if (p.num_splits == 1) {
+      p.out[((int64_t)b * p.Hq + head) * Dv + dv] = float_to_half<BF16>(O * inv);
+    } else {
+      p.part_o[(((int64_t)b * p.Hq + head) * p.num_splits + split) * Dv + dv] = O * inv;
+      if (dv == 0) p.part_lse[((int64_t)b * p.Hq + head) * p.num_splits + split] = L > 0.f ? M + log2f(L) : -INFINITY;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// generic SIMT kernel: any D, Dv <= 32*MAXE (MLA 576/512, odd head sizes of the reference tests).
+// grid = (split, Hq, B), 4 warps; warp w handles tokens kv0 + w, kv0 + w + 4, ...
+// ------------------------------------------------------------------------------------------------
+template <int MAXE, bool BF16>
+__global__ void __launch_bounds__(128) decode_attn_generic_kernel(const __grid_constant__ DecodeKParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int kvh = h / p.G;
+  const int D = p.D, Dv = p.Dv;
+  const int64_t len = p.seq_lens[b], req = p.rpi[b];
+  const int64_t loc_b = p.fused_new ? p.loc[b] : -1;
+  const int64_t per = (len + p.num_splits - 1) / p.num_splits;
+  const int64_t kv0 = (int64_t)split * per;
+  const int64_t kv1 = (kv0 + per < len) ? kv0 + per : len;
+  __shared__ float sm_o[4][32 * MAXE];
+  __shared__ float sm_ml[4][2];
+
+  if (p.fused_new && split == 0 && (h % p.G) == 0) {
+    // fused set_kv_buffer for kv head kvh (MLA: k only, v aliases k)
+    const uint16_t* ks = p.k_new + b * p.kn_sb + kvh * p.kn_sh;
+    uint16_t* kd = p.k_buf + loc_b * p.kb_st + kvh * p.kb_sh;
+    for (int i = threadIdx.x; i < D; i += 128) kd[i] = ks[i];
+    if (!p.is_mla) {
+      const uint16_t* vs = p.v_new + b * p.vn_sb + kvh * p.vn_sh;
+      uint16_t* vd = p.v_buf + loc_b * p.vb_st + kvh * p.vb_sh;
+      for (int i = threadIdx.x; i < Dv; i += 128) vd[i] = vs[i];
+    }
+  }
+
+  float qr[MAXE], acc[MAXE];
+#pragma unroll
+  for (int e = 0; e < MAXE; ++e) {
+    const int d = e * 32 + lane;
+    qr[e] = d < D ? half_to_float<BF16>(p.q[b * p.q_sb + (int64_t)h * p.q_sh + d]) : 0.f;
+    acc[e] = 0.f;
+  }
+  float m_run = -INFINITY, l_run = 0.f;
+  const bool has_cap = p.logit_cap > 0.f;
+  for (int64_t pos = kv0 + warp; pos < kv1; pos += 4) {
+    const int64_t idx = load_index(p.r2t, req * p.r2t_stride + pos, p.idx64);
+    const uint16_t* kr = p.k_buf + idx * p.kb_st + kvh * p.kb_sh;
+    const uint16_t* vr = p.v_buf + idx * p.vb_st + kvh * p.vb_sh;
+    if (idx == loc_b) {
+      kr = p.k_new + b * p.kn_sb + kvh * p.kn_sh;
+      vr = p.is_mla ? kr : p.v_new + b * p.vn_sb + kvh * p.vn_sh;
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int e = 0; e < MAXE; ++e) {
+      const int d = e * 32 + lane;
+      if (d < D) s += qr[e] * half_to_float<BF16>(kr[d]);
+    }
+    s = warp_sum(s) * p.sm_scale;
+    if (has_cap) s = p.logit_cap * tanhf(s / p.logit_cap);
+    s *= kLog2e;
+    const float m_new = fmaxf(m_run, s);
+    const float alpha = exp2f(m_run - m_new);
+    float pr = exp2f(s - m_new);
+    l_run = l_run * alpha + pr;
+    if (p.is_mla) pr = half_to_float<BF16>(float_to_half<BF16>(pr));  // decode.cpp:1157-1159
+    m_run = m_new;
+#pragma unroll
+    for (int e = 0; e < MAXE; ++e) {
+      const int d = e * 32 + lane;
+      if (d < Dv) acc[e] = acc[e] * alpha + pr * half_to_float<BF16>(vr[d]);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < MAXE; ++e) sm_o[warp][e * 32 + lane] = acc[e];
+  if (lane == 0) {
+    sm_ml[warp][0] = m_run;
+    sm_ml[warp][1] = l_run;
+  }
+  __syncthreads();
+  float M = fmaxf(fmaxf(sm_ml[0][0], sm_ml[1][0]), fmaxf(sm_ml[2][0], sm_ml[3][0]));
+  const float Mu = (M == -INFINITY) ? 0.f : M;
+  float w[4], L = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    w[i] = exp2f(sm_ml[i][0] - Mu);
+    L += sm_ml[i][1] * w[i];
+  }
+  const float inv = L > 0.f ? 1.f / L : 0.f;
+  for (int d = threadIdx.x; d < Dv; d += 128) {
+    const float O = sm_o[0][d] * w[0] + sm_o[1][d] * w[1] + sm_o[2][d] * w[2] + sm_o[3][d] * w[3];
+    if (p.num_splits == 1)
+      p.out[((int64_t)b * p.Hq + h) * Dv + d] = float_to_half<BF16>(O * inv);
+    else
+      p.part_o[(((int64_t)b * p.Hq + h) * p.num_splits + split) * Dv + d] = O * inv;
+  }
+  if (threadIdx.x == 0 && p.num_splits > 1)
+    p.part_lse[((int64_t)b * p.Hq + h) * p.num_splits + split] = L > 0.f ? M + log2f(L) : -INFINITY;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LSE merge of the KV splits (decode.cpp:812-860 decode_accumulate_kv_splits;
+// decode_attention.py:492-552 _fwd_kernel_stage2).  grid = B*Hq, block = 128.
+// ------------------------------------------------------------------------------------------------
+template <bool BF16>
+__global__ void __launch_bounds__(128) decode_merge_kernel(const float* __restrict__ part_o,
+                                                           const float* __restrict__ part_lse, uint16_t* __restrict__ out,
+                                                           int S, int Dv) {
+  const int64_t bh = blockIdx.x;
+  const float* lse = part_lse + bh * S;
+  float M = -INFINITY;
+  for (int s = 0; s < S; ++s) M = fmaxf(M, lse[s]);
+  const float Mu = (M == -INFINITY) ? 0.f : M;
+  float L = 0.f;
+  for (int s = 0; s < S; ++s) L += exp2f(lse[s] - Mu);
+  const float inv = L > 0.f ? 1.f / L : 0.f;
+  for (int d = threadIdx.x; d < Dv; d += 128) {
+    float acc = 0.f;
+    for (int s = 0; s < S; ++s) {
+      const float w = exp2f(lse[s] - Mu);
+      if (w > 0.f) acc += w * part_o[(bh * S + s) * Dv + d];
+    }
+    out[bh * Dv + d] = float_to_half<BF16>(acc * inv);
+  }
+}
+
+// KVCache.set_kv_buffer (memory_pool.py:418-456 / decode.cpp:771-809): grid = (B, Hkv), 16-bit elements
+__global__ void set_kv_kernel(uint16_t* k_buf, int64_t kb_st, int64_t kb_sh, uint16_t* v_buf, int64_t vb_st,
+                              int64_t vb_sh, const uint16_t* k_new, int64_t kn_sb, int64_t kn_sh, const uint16_t* v_new,
+                              int64_t vn_sb, int64_t vn_sh, const int64_t* loc, int D, int Dv) {
+  const int b = blockIdx.x, h = blockIdx.y;
+  const int64_t l = loc[b];
+  if (k_new) {
+    const uint16_t* s = k_new + b * kn_sb + h * kn_sh;
+    uint16_t* d = k_buf + l * kb_st + h * kb_sh;
+    for (int i = threadIdx.x; i < D; i += blockDim.x) d[i] = s[i];
+  }
+  if (v_new) {
+    const uint16_t* s = v_new + b * vn_sb + h * vn_sh;
+    uint16_t* d = v_buf + l * vb_st + h * vb_sh;
+    for (int i = threadIdx.x; i < Dv; i += blockDim.x) d[i] = s[i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static int pick_hpc(int Hkv) {
+  if (Hkv % 8 == 0) return 8;
+  if (Hkv % 4 == 0) return 4;
+  if (Hkv % 2 == 0) return 2;
+  return 1;
+}
+
+static bool mma_path_ok(int Hq, int Hkv, int D, int Dv) { return D == Dv && (D == 64 || D == 128) && Hq % Hkv == 0; }
+
+static int choose_splits(int B, int ctas_per_req, int max_seq_len, int tile_t, int hint) {
+  if (hint > 0) return hint > 64 ? 64 : hint;
+  if (max_seq_len <= 0) max_seq_len = 4096;
+  const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
+  int min_tok = 2 * tile_t > 256 ? 2 * tile_t : 256;
+  int max_s = max_seq_len / min_tok;
+  if (max_s < 1) max_s = 1;
+  if (max_s > 32) max_s = 32;
+  double best = -1.0;
+  int best_s = 1;
+  for (int s = 1; s <= max_s; ++s) {
+    const double ctas = (double)B * ctas_per_req * s;
+    const double waves = ceil(ctas / sms);
+    const double util = ctas / (waves * sms) - 0.004 * s;  // mild bias towards fewer splits
+    if (util > best + 1e-9) {
+      best = util;
+      best_s = s;
+    }
+  }
+  return best_s;
+}
+
+template <int D, int HPC, bool BF16>
+static int launch_mma(const DecodeKParams& kp, cudaStream_t st) {
+  using C = AttnCfg<D, HPC>;
+  auto kern = decode_attn_mma_kernel<D, HPC, BF16>;
+  static bool configured = false;
+  if (!configured) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    configured = true;
+  }
+  const int n_qblk = (kp.G + 15) / 16;
+  dim3 grid(kp.num_splits, (kp.Hkv / HPC) * n_qblk, kp.B);
+  kern<<<grid, kAttnThreads, C::SMEM_BYTES, st>>>(kp);
+  return check_cuda(cudaGetLastError(), "decode_attn_mma_kernel launch");
+}
+
+template <bool BF16>
+static int dispatch_mma(const DecodeKParams& kp, int hpc, cudaStream_t st) {
+#define B200_CASE(DD, HH) \
+  if (kp.D == DD && hpc == HH) return launch_mma<DD, HH, BF16>(kp, st);
+  B200_CASE(128, 8) B200_CASE(128, 4) B200_CASE(128, 2) B200_CASE(128, 1)
+  B200_CASE(64, 8) B200_CASE(64, 4) B200_CASE(64, 2) B200_CASE(64, 1)
+#undef B200_CASE
+  set_error("decode_attn: no mma instantiation for D=%d hpc=%d", kp.D, hpc);
+  return B200_ERR_UNSUPPORTED;
+}
+
+template <bool BF16>
+static int launch_generic(const DecodeKParams& kp, cudaStream_t st) {
+  dim3 grid(kp.num_splits, kp.Hq, kp.B);
+  const int mx = kp.D > kp.Dv ? kp.D : kp.Dv;
+  if (mx <= 128) decode_attn_generic_kernel<4, BF16><<<grid, 128, 0, st>>>(kp);
+  else if (mx <= 256) decode_attn_generic_kernel<8, BF16><<<grid, 128, 0, st>>>(kp);
+  else if (mx <= 640) decode_attn_generic_kernel<20, BF16><<<grid, 128, 0, st>>>(kp);
+  else decode_attn_generic_kernel<32, BF16><<<grid, 128, 0, st>>>(kp);
+  return check_cuda(cudaGetLastError(), "decode_attn_generic_kernel launch");
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv, int max_seq_len, int num_splits_hint) {
+  if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv != 0) return 1;
+  if (mma_path_ok(Hq, Hkv, D, Dv)) {
+    const int hpc = pick_hpc(Hkv);
+    const int G = Hq / Hkv;
+    return choose_splits(B, (Hkv / hpc) * ((G + 15) / 16), max_seq_len, (kConsumerWarps / hpc) * kTokPerWarp,
+                         num_splits_hint);
+  }
+  // generic path: 128-thread CTAs, many per SM -> aim for >= 8 CTAs per SM
+  if (num_splits_hint > 0) return num_splits_hint > 64 ? 64 : num_splits_hint;
+  if (max_seq_len <= 0) max_seq_len = 4096;
+  const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
+  int s = (8 * sms + B * Hq - 1) / (B * Hq);
+  int max_s = max_seq_len / 64;
+  if (max_s < 1) max_s = 1;
+  if (s > max_s) s = max_s;
+  if (s > 32) s = 32;
+  if (s < 1) s = 1;
+  return s;
+}
+
+extern "C" size_t b200_decode_attn_workspace_size(int B, int Hq, int Dv, int num_splits) {
+  if (num_splits <= 1) return 16;
+  return ((size_t)B * Hq * num_splits * (Dv + 1)) * sizeof(float) + 256;
+}
+
+extern "C" int b200_set_kv_buffer(void* k_buf, int64_t kb_st, int64_t kb_sh, void* v_buf, int64_t vb_st, int64_t vb_sh,
+                                  const void* k_new, int64_t kn_sb, int64_t kn_sh, const void* v_new, int64_t vn_sb,
+                                  int64_t vn_sh, const int64_t* loc, int B, int Hkv, int D, int Dv, int elem_bytes,
+                                  void* stream) {
+  B200_REQUIRE(elem_bytes == 2, B200_ERR_UNSUPPORTED, "set_kv_buffer: only 16-bit KV dtypes are supported");
+  B200_REQUIRE(B >= 0 && Hkv > 0 && D > 0, B200_ERR_ARG, "set_kv_buffer: bad sizes");
+  if (B == 0) return B200_OK;
+  set_kv_kernel<<<dim3(B, Hkv), 128, 0, (cudaStream_t)stream>>>(
+      (uint16_t*)k_buf, kb_st, kb_sh, (uint16_t*)v_buf, vb_st, vb_sh, (const uint16_t*)k_new, kn_sb, kn_sh,
+      (const uint16_t*)v_new, vn_sb, vn_sh, loc, D, Dv);
+  return check_cuda(cudaGetLastError(), "set_kv_kernel launch");
+}
+
+extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) {
+  B200_REQUIRE(a != nullptr, B200_ERR_ARG, "decode_attn: null params");
+  B200_REQUIRE(a->B >= 0 && a->Hq > 0 && a->Hkv > 0 && a->D > 0 && a->Dv > 0, B200_ERR_ARG, "decode_attn: bad sizes");
+  B200_REQUIRE(a->Hq % a->Hkv == 0, B200_ERR_ARG, "decode_attn: Hq %% Hkv != 0");
+  B200_REQUIRE(a->dtype == B200_BF16 || a->dtype == B200_F16, B200_ERR_UNSUPPORTED, "decode_attn: dtype must be bf16/f16");
+  B200_REQUIRE(a->D <= 1024 && a->Dv <= 1024, B200_ERR_UNSUPPORTED, "decode_attn: head dim > 1024");
+  B200_REQUIRE(a->q && a->k_buf && a->v_buf && a->out && a->req_to_token && a->req_pool_indices && a->seq_lens,
+               B200_ERR_ARG, "decode_attn: null tensor");
+  if (a->B == 0) return B200_OK;
+  const int arch = b200_sm_arch();
+  B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "decode_attn: requires an sm_100 device (got sm_%d); no fallback", arch);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool is_mla = (a->k_buf == a->v_buf && a->Hkv == 1 && a->D == a->Dv + 64);  // decode.cpp:1455
+  B200_REQUIRE(!(is_mla && a->logit_cap != 0.f), B200_ERR_ARG, "decode MLA: expect no logit_cap (decode.cpp:1042)");
+  int write_kv = a->write_kv;
+  if (write_kv) {
+    B200_REQUIRE(a->k_new && (is_mla || a->v_new) && a->out_cache_loc, B200_ERR_ARG, "decode_attn: write_kv needs k_new/v_new/out_cache_loc");
+  }
+
+  DecodeKParams kp;
+  kp.q = (const uint16_t*)a->q; kp.q_sb = a->q_stride_b; kp.q_sh = a->q_stride_h;
+  kp.k_new = (const uint16_t*)a->k_new; kp.kn_sb = a->knew_stride_b; kp.kn_sh = a->knew_stride_h;
+  kp.v_new = (const uint16_t*)a->v_new; kp.vn_sb = a->vnew_stride_b; kp.vn_sh = a->vnew_stride_h;
+  kp.k_buf = (uint16_t*)a->k_buf; kp.kb_st = a->kbuf_stride_t; kp.kb_sh = a->kbuf_stride_h;
+  kp.v_buf = (uint16_t*)a->v_buf; kp.vb_st = a->vbuf_stride_t; kp.vb_sh = a->vbuf_stride_h;
+  kp.out = (uint16_t*)a->out;
+  kp.r2t = a->req_to_token; kp.r2t_stride = a->req_to_token_stride; kp.idx64 = a->idx_is_i64;
+  kp.rpi = a->req_pool_indices; kp.seq_lens = a->seq_lens; kp.loc = a->out_cache_loc;
+  kp.B = a->B; kp.Hq = a->Hq; kp.Hkv = a->Hkv; kp.G = a->Hq / a->Hkv; kp.D = a->D; kp.Dv = a->Dv;
+  kp.is_mla = is_mla; kp.sm_scale = a->sm_scale; kp.logit_cap = a->logit_cap;
+
+  // tuned path needs 16-byte aligned, head-contiguous rows
+  bool mma = mma_path_ok(a->Hq, a->Hkv, a->D, a->Dv);
+  int hpc = pick_hpc(a->Hkv);
+  if (mma) {
+    auto al16 = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
+    const bool rows_ok = al16(a->k_buf) && al16(a->v_buf) && a->kbuf_stride_t % 8 == 0 && a->vbuf_stride_t % 8 == 0 &&
+                         a->kbuf_stride_h % 8 == 0 && a->vbuf_stride_h % 8 == 0;
+    const bool q_ok = ((uintptr_t)a->q & 3) == 0 && a->q_stride_b % 2 == 0 && a->q_stride_h % 2 == 0;
+    if (!rows_ok || !q_ok) mma = false;
+    if (mma && hpc > 1 && (a->kbuf_stride_h != a->D || a->vbuf_stride_h != a->Dv)) hpc = 1;  // heads not adjacent
+  }
+  // fused append (write_kv == 2) needs aligned, head-contiguous new rows on the tuned path
+  bool fused = (write_kv == 2);
+  if (fused && mma) {
+    auto al16 = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
+    const bool new_ok = al16(a->k_new) && al16(a->v_new) && a->knew_stride_b % 8 == 0 && a->vnew_stride_b % 8 == 0 &&
+                        a->knew_stride_h % 8 == 0 && a->vnew_stride_h % 8 == 0 &&
+                        (hpc == 1 || (a->knew_stride_h == a->D && a->vnew_stride_h == a->Dv));
+    if (!new_ok) fused = false;
+  }
+  if (write_kv && !fused) {
+    int rc = b200_set_kv_buffer(a->k_buf, a->kbuf_stride_t, a->kbuf_stride_h, a->v_buf, a->vbuf_stride_t,
+                                a->vbuf_stride_h, a->k_new, a->knew_stride_b, a->knew_stride_h,
+                                is_mla ? nullptr : a->v_new, a->vnew_stride_b, a->vnew_stride_h, a->out_cache_loc,
+                                a->B, a->Hkv, a->D, a->Dv, 2, stream);
+    if (rc != 0) return rc;
+  }
+  kp.fused_new = fused ? 1 : 0;
+
+  int S;
+  if (mma) {
+    S = choose_splits(a->B, (a->Hkv / hpc) * ((kp.G + 15) / 16), a->max_seq_len, (kConsumerWarps / hpc) * kTokPerWarp,
+                      a->num_splits);
+  } else {
+    S = b200_decode_attn_num_splits(a->B, a->Hq, a->Hkv, a->D, a->Dv, a->max_seq_len, a->num_splits);
+  }
+  kp.num_splits = S;
+  kp.part_o = nullptr; kp.part_lse = nullptr;
+  if (S > 1) {
+    const size_t need = b200_decode_attn_workspace_size(a->B, a->Hq, a->Dv, S);
+    B200_REQUIRE(a->workspace && a->workspace_bytes >= need && ((uintptr_t)a->workspace & 15) == 0, B200_ERR_ARG,
+                 "decode_attn: workspace too small or misaligned (need %zu bytes, have %zu)", need, a->workspace_bytes);
+    kp.part_o = (float*)a->workspace;
+    kp.part_lse = kp.part_o + (size_t)a->B * a->Hq * S * a->Dv;
+  }
+  int rc;
+  if (mma) rc = a->dtype == B200_BF16 ? dispatch_mma<true>(kp, hpc, st) : dispatch_mma<false>(kp, hpc, st);
+  else rc = a->dtype == B200_BF16 ? launch_generic<true>(kp, st) : launch_generic<false>(kp, st);
+  if (rc != 0) return rc;
+  if (S > 1) {
+    if (a->dtype == B200_BF16)
+      decode_merge_kernel<true><<<a->B * a->Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, S, a->Dv);
+    else
+      decode_merge_kernel<false><<<a->B * a->Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, S, a->Dv);
+    return check_cuda(cudaGetLastError(), "decode_merge_kernel launch");
+  }
+  return B200_OK;
+}

@@ -1,0 +1,92 @@
+// C-ABI plumbing: thread-local error string, device queries, TMA descriptor encoding.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return 0;
+  set_error("CUDA error in %s: %s", what, cudaGetErrorString(e));
+  return B200_ERR_CUDA;
+}
+
+int device_sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+PFN_encodeTiled get_encode_tiled() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+int make_tmap_2d(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int elem_bytes, uint64_t rows,
+                 uint64_t cols, uint64_t ld_bytes, uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz) {
+  PFN_encodeTiled enc = get_encode_tiled();
+  B200_REQUIRE(enc != nullptr, B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  B200_REQUIRE(((uintptr_t)ptr & 15) == 0 && ld_bytes % 16 == 0, B200_ERR_ARG,
+               "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch (ptr=%p pitch=%llu)", ptr,
+               (unsigned long long)ld_bytes);
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_bytes};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  (void)elem_bytes;
+  CUresult r = enc(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" const char* b200_last_error(void) { return b200::g_err; }
+extern "C" int b200_abi_version(void) { return B200_SGL_ABI_VERSION; }
+
+extern "C" int b200_sm_arch(void) {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    b200::set_error("cudaGetDevice failed: %s", cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+  }
+  if (dev >= 0 && dev < 64 && cached[dev]) return cached[dev];
+  int major = 0, minor = 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev) != cudaSuccess) {
+    b200::set_error("cudaDeviceGetAttribute(compute capability) failed");
+    return B200_ERR_CUDA;
+  }
+  const int arch = major * 10 + minor;
+  if (dev >= 0 && dev < 64) cached[dev] = arch;
+  return arch;
+}
+
+extern "C" int b200_sm_count(void) { return b200::device_sm_count(); }

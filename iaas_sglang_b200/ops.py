@@ -1,0 +1,443 @@
+"""Kernel ops with the reference's sgl_kernel signatures, backed by the sm_100a C-ABI library.
+
+Mirrors sgl-kernel/python/sgl_kernel/gemm.py:7-31 (awq_dequantize, int8_scaled_mm,
+fp8_blockwise_scaled_mm), python/sglang/srt/layers/quantization/fp8_kernel.py:273-326
+(sglang_per_token_group_quant_fp8), int8_kernel.py:51-81 (per_token_quant_int8) and
+python/sglang/srt/layers/attention/utils.py (kv index builders): same positional arguments, same
+returned shapes/dtypes/strides, same precondition errors.  Each op allocates its output with
+torch.empty and enqueues the kernel on the current CUDA stream; nothing synchronises.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import DTYPE_CODE, c_float, c_int, c_int64, c_size_t, check, current_stream, load, ptr, require_cuda
+
+fp8_dtype = torch.float8_e4m3fn
+FP8_MAX = 448.0
+
+# ---------------------------------------------------------------------------------------------
+# scratch: one zero-initialised split-K workspace per device (tile tickets are self-resetting)
+# ---------------------------------------------------------------------------------------------
+_gemm_ws: Dict[torch.device, torch.Tensor] = {}
+
+
+def gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    ws = _gemm_ws.get(device)
+    if ws is None or ws.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("iaas_sglang_b200: GEMM workspace must be sized before CUDA-graph capture "
+                               "(call ops.reserve_gemm_workspace)")
+        ws = torch.zeros(max(nbytes, 32 << 20), dtype=torch.uint8, device=device)
+        _gemm_ws[device] = ws
+    return ws
+
+
+def reserve_gemm_workspace(device, nbytes: int) -> None:
+    gemm_workspace(torch.device(device), nbytes)
+
+
+# ---------------------------------------------------------------------------------------------
+# quantised GEMMs
+# ---------------------------------------------------------------------------------------------
+def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor, scales_b: torch.Tensor,
+                            out_dtype: torch.dtype) -> torch.Tensor:
+    """sgl_kernel.fp8_blockwise_scaled_mm (gemm.py:24-31; fp8_blockwise_gemm_kernel.cu:345-423).
+
+    mat_a [M,K] e4m3 row-major; mat_b [K,N] e4m3 column-major; scales_a [M,K/128] f32 M-major;
+    scales_b [K/128,N/128] f32 K-major; returns [M,N] out_dtype.  Checks follow :351-383."""
+    dev = require_cuda(mat_a, mat_b, scales_a, scales_b)
+    if mat_a.dim() != 2 or mat_b.dim() != 2:
+        raise RuntimeError("mat_a and mat_b must be a matrix")
+    if mat_a.stride(1) != 1:
+        raise RuntimeError("mat_a must be a row major tensor")
+    if mat_b.stride(0) != 1:
+        raise RuntimeError("mat_b must be a column major tensor")
+    if mat_a.shape[1] != mat_b.shape[0]:
+        raise RuntimeError("mat_a and mat_b shapes cannot be multiplied")
+    if mat_a.dtype != fp8_dtype or mat_b.dtype != fp8_dtype:
+        raise RuntimeError("mat_a and mat_b must be Float8_e4m3fn")
+    if out_dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError("out_dtype must be Half or BFloat16")
+    M, K = mat_a.shape
+    N = mat_b.shape[1]
+    kb, nb = (K + 127) // 128, (N + 127) // 128
+    if scales_a.dtype != torch.float32 or scales_b.dtype != torch.float32:
+        raise RuntimeError("scales_a and scales_b must be Float32")
+    if tuple(scales_a.shape) != (M, kb):
+        raise RuntimeError(f"scales_a must be [M, K/128] = {(M, kb)}, got {tuple(scales_a.shape)}")
+    if tuple(scales_b.shape) != (kb, nb):
+        raise RuntimeError(f"scales_b must be [K/128, N/128] = {(kb, nb)}, got {tuple(scales_b.shape)}")
+    if M > 1 and kb > 1 and scales_a.stride(0) != 1:
+        raise RuntimeError("scales_a must be M major")
+    if kb > 1 and nb > 1 and scales_b.stride(0) != 1:
+        raise RuntimeError("scales_b must be K major")
+    out = torch.empty((M, N), dtype=out_dtype, device=dev)
+    if M == 0:
+        return out
+    lib = load()
+    nbytes = lib.b200_gemm_workspace_size(M, N, K)
+    ws = gemm_workspace(dev, nbytes)
+    with torch.cuda.device(dev):
+        check(lib.b200_fp8_blockwise_scaled_mm(
+            ptr(mat_a), mat_a.stride(0), ptr(mat_b), mat_b.stride(1), ptr(scales_a), scales_a.stride(0),
+            scales_a.stride(1), ptr(scales_b), scales_b.stride(0), scales_b.stride(1), ptr(out), out.stride(0),
+            DTYPE_CODE[out_dtype], M, N, K, ptr(ws), ws.numel(), current_stream(dev)))
+    return out
+
+
+def int8_scaled_mm(mat_a, mat_b, scales_a, scales_b, out_dtype, bias=None) -> torch.Tensor:
+    """sgl_kernel.int8_scaled_mm (gemm.py:13-21; int8_gemm_kernel.cu:663-747). The reference has no
+    sm_100 path for this op (:724-743 raises on B200); this one runs on tcgen05 kind::i8."""
+    dev = require_cuda(mat_a, mat_b, scales_a, scales_b, bias)
+    if mat_a.dim() != 2 or mat_b.dim() != 2:
+        raise RuntimeError("mat_a and mat_b must be a matrix")
+    if mat_a.stride(1) != 1:
+        raise RuntimeError("mat_a must be a row major tensor")
+    if mat_b.stride(0) != 1:
+        raise RuntimeError("mat_b must be a column major tensor")
+    if mat_a.shape[1] != mat_b.shape[0]:
+        raise RuntimeError("mat_a and mat_b shapes cannot be multiplied")
+    if mat_a.dtype != torch.int8 or mat_b.dtype != torch.int8:
+        raise RuntimeError("mat_a and mat_b must be Int8")
+    if out_dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError("out_dtype must be Half or BFloat16")
+    M, K = mat_a.shape
+    N = mat_b.shape[1]
+    if scales_a.numel() != M or scales_b.numel() != N:
+        raise RuntimeError("size of scales_a / scales_b is not matched")
+    if not scales_a.is_contiguous() or not scales_b.is_contiguous():
+        raise RuntimeError("scales_a and scales_b must be contiguous")
+    if scales_a.dtype != torch.float32 or scales_b.dtype != torch.float32:
+        raise RuntimeError("scales_a and scales_b must be Float32")
+    if bias is not None:
+        if bias.numel() != N or not bias.is_contiguous() or bias.dtype != out_dtype:
+            raise RuntimeError("bias must be a contiguous [N] tensor of out_dtype")
+    out = torch.empty((M, N), dtype=out_dtype, device=dev)
+    if M == 0:
+        return out
+    lib = load()
+    ws = gemm_workspace(dev, lib.b200_gemm_workspace_size(M, N, K))
+    with torch.cuda.device(dev):
+        check(lib.b200_int8_scaled_mm(ptr(mat_a), mat_a.stride(0), ptr(mat_b), mat_b.stride(1), ptr(scales_a),
+                                      ptr(scales_b), ptr(bias), ptr(out), out.stride(0), DTYPE_CODE[out_dtype], M, N, K,
+                                      ptr(ws), ws.numel(), current_stream(dev)))
+    return out
+
+
+def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """sgl_kernel.awq_dequantize (gemm.py:7-10; awq_kernel.cu:186-221) -> [rows, cols*8] of scales.dtype."""
+    dev = require_cuda(qweight, scales, qzeros)
+    if qweight.dtype != torch.int32 or qzeros.dtype != torch.int32:
+        raise RuntimeError("qweight and qzeros must be Int32")
+    if scales.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError("scales must be Half or BFloat16")
+    rows, cols = qweight.shape
+    group = rows // scales.shape[0]
+    qweight, scales, qzeros = qweight.contiguous(), scales.contiguous(), qzeros.contiguous()
+    out = torch.empty((rows, cols * 8), dtype=scales.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(load().b200_awq_dequantize(ptr(qweight), ptr(scales), ptr(qzeros), ptr(out), DTYPE_CODE[scales.dtype], rows,
+                                         cols, group, current_stream(dev)))
+    return out
+
+
+_awq_ws: Dict[torch.device, torch.Tensor] = {}
+
+
+def awq_w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor,
+                   bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """AWQLinearMethod.apply's math (awq.py:186-204): x @ dequant(qweight) (+ bias) on our own kernels."""
+    dev = require_cuda(x, qweight, scales, qzeros, bias)
+    if x.dim() != 2 or x.stride(1) != 1:
+        raise RuntimeError("x must be a row major matrix")
+    if x.dtype != scales.dtype or x.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError("x and scales must share a Half/BFloat16 dtype")
+    M, K = x.shape
+    if qweight.shape[0] != K:
+        raise RuntimeError("x and qweight shapes cannot be multiplied")
+    N = qweight.shape[1] * 8
+    group = K // scales.shape[0]
+    qweight, scales, qzeros = qweight.contiguous(), scales.contiguous(), qzeros.contiguous()
+    out = torch.empty((M, N), dtype=x.dtype, device=dev)
+    if M == 0:
+        return out
+    lib = load()
+    need = lib.b200_awq_w4a16_workspace_size(M, N, K)
+    ws = _awq_ws.get(dev)
+    if ws is None or ws.numel() < need:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("iaas_sglang_b200: AWQ workspace must be sized before CUDA-graph capture")
+        ws = torch.zeros(need, dtype=torch.uint8, device=dev)
+        _awq_ws[dev] = ws
+    with torch.cuda.device(dev):
+        check(lib.b200_awq_w4a16_mm(ptr(x), x.stride(0), ptr(qweight), ptr(scales), ptr(qzeros), ptr(bias), ptr(out),
+                                    out.stride(0), DTYPE_CODE[x.dtype], M, N, K, group, ptr(ws), ws.numel(),
+                                    current_stream(dev)))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# activation quantisation
+# ---------------------------------------------------------------------------------------------
+def sgl_per_token_group_quant_fp8(input: torch.Tensor, output_q: torch.Tensor, output_s: torch.Tensor, group_size: int,
+                                  eps: float, fp8_min: float, fp8_max: float, scale_ue8m0: bool = False) -> None:
+    """torch.ops.sgl_kernel.sgl_per_token_group_quant_fp8 (common_extension.cc:116-119): in-place form."""
+    dev = require_cuda(input, output_q, output_s)
+    if scale_ue8m0:
+        raise NotImplementedError("scale_ue8m0 (DeepGEMM packed scales) is outside the hot path (SURVEY 2.1 #19)")
+    if input.stride(-1) != 1 or output_q.stride(-1) != 1:
+        raise RuntimeError("input and output_q must be contiguous in the last dimension")
+    x2 = input.reshape(-1, input.shape[-1])
+    q2 = output_q.view(-1, output_q.shape[-1])
+    s2 = output_s.view(-1, output_s.shape[-1]) if output_s.dim() != 2 else output_s
+    M, K = x2.shape
+    with torch.cuda.device(dev):
+        check(load().b200_per_token_group_quant_fp8(ptr(x2), x2.stride(0), DTYPE_CODE[x2.dtype], ptr(q2), q2.stride(0),
+                                                    ptr(s2), s2.stride(0), s2.stride(1), M, K, group_size, eps, fp8_min,
+                                                    fp8_max, current_stream(dev)))
+
+
+def per_token_group_quant_fp8(x: torch.Tensor, group_size: int = 128, eps: float = 1e-10,
+                              column_major_scales: bool = False, scale_tma_aligned: bool = False,
+                              scale_ue8m0: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    """sglang_per_token_group_quant_fp8 (fp8_kernel.py:273-326) -> (x_q e4m3, x_s f32 [.., K/group])."""
+    assert x.shape[-1] % group_size == 0, "the last dimension of `x` cannot be divisible by `group_size`"
+    assert x.is_contiguous(), "`x` is not contiguous"
+    if scale_ue8m0:
+        raise NotImplementedError("scale_ue8m0 is outside the hot path")
+    x_q = torch.empty_like(x, dtype=fp8_dtype)
+    M = x.numel() // x.shape[-1]
+    G = x.shape[-1] // group_size
+    if column_major_scales:
+        if scale_tma_aligned:
+            aligned = (M + 3) // 4 * 4
+            x_s = torch.empty((G, aligned), dtype=torch.float32, device=x.device).t()[:M, :]
+        else:
+            x_s = torch.empty((G, M), dtype=torch.float32, device=x.device).t()
+    else:
+        x_s = torch.empty((M, G), dtype=torch.float32, device=x.device)
+    if x.numel() > 0:
+        sgl_per_token_group_quant_fp8(x, x_q, x_s, group_size, eps, -FP8_MAX, FP8_MAX, False)
+    if x.dim() != 2:
+        x_s = x_s.reshape(x.shape[:-1] + (G,)) if not column_major_scales else x_s
+    return x_q, x_s
+
+
+def per_token_quant_int8(x: torch.Tensor, scale_dtype=torch.float32, cal_sum: bool = False):
+    """per_token_quant_int8 (int8_kernel.py:51-81) -> (x_q int8, scales [..,1] f32)."""
+    dev = require_cuda(x)
+    assert x.is_contiguous()
+    if cal_sum:
+        raise NotImplementedError("cal_sum is only used by the w8a8-fp8/int8 zero-point paths (out of scope)")
+    if scale_dtype != torch.float32:
+        raise NotImplementedError("per_token_quant_int8: only float32 scales")
+    x2 = x.view(-1, x.shape[-1])
+    M, K = x2.shape
+    x_q = torch.empty_like(x, dtype=torch.int8)
+    scales = torch.empty(x.shape[:-1] + (1,), device=dev, dtype=torch.float32)
+    if M > 0:
+        with torch.cuda.device(dev):
+            check(load().b200_per_token_quant_int8(ptr(x2), x2.stride(0), DTYPE_CODE[x.dtype], ptr(x_q), K, ptr(scales), M,
+                                                   K, current_stream(dev)))
+    return x_q, scales
+
+
+# ---------------------------------------------------------------------------------------------
+# page-table index builders
+# ---------------------------------------------------------------------------------------------
+def _i64(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    if t is None:
+        return None
+    return t if t.dtype == torch.int64 and t.is_contiguous() else t.to(torch.int64).contiguous()
+
+
+def create_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, page_kernel_lens: torch.Tensor,
+                      kv_indptr: torch.Tensor, kv_start_idx: Optional[torch.Tensor], kv_indices: torch.Tensor) -> None:
+    """create_flashinfer_kv_indices_triton[(bs,)](...) (attention/utils.py:5-41); writes kv_indices in place."""
+    dev = require_cuda(req_to_token, req_pool_indices, page_kernel_lens, kv_indptr, kv_indices)
+    if kv_indices.dtype != torch.int32 or req_to_token.dtype not in (torch.int32, torch.int64):
+        raise RuntimeError("kv_indices must be int32 and req_to_token int32/int64")
+    if req_to_token.stride(1) != 1:
+        raise RuntimeError("req_to_token rows must be contiguous")
+    rpi, lens, ip, ks = _i64(req_pool_indices), _i64(page_kernel_lens), _i64(kv_indptr), _i64(kv_start_idx)
+    with torch.cuda.device(dev):
+        check(load().b200_create_kv_indices(ptr(req_to_token), int(req_to_token.dtype == torch.int64),
+                                            req_to_token.stride(0), ptr(rpi), ptr(lens), ptr(ip), ptr(ks), ptr(kv_indices),
+                                            rpi.numel(), current_stream(dev)))
+
+
+def create_page_table(req_to_token, req_pool_indices, page_kernel_lens, kv_start_idx, kv_indices: torch.Tensor,
+                      page_size: int) -> None:
+    """create_flashmla_kv_indices_triton[(bs,)](...) (attention/utils.py:44-94); kv_indices [B, max_pages] int32."""
+    dev = require_cuda(req_to_token, req_pool_indices, page_kernel_lens, kv_indices)
+    rpi, lens, ks = _i64(req_pool_indices), _i64(page_kernel_lens), _i64(kv_start_idx)
+    with torch.cuda.device(dev):
+        check(load().b200_create_page_table(ptr(req_to_token), int(req_to_token.dtype == torch.int64),
+                                            req_to_token.stride(0), ptr(rpi), ptr(lens), ptr(ks), ptr(kv_indices),
+                                            kv_indices.stride(0), rpi.numel(), page_size, kv_indices.shape[1],
+                                            current_stream(dev)))
+
+
+# ---------------------------------------------------------------------------------------------
+# attention (functional forms; the plugin class is backend.B200AttnBackend)
+# ---------------------------------------------------------------------------------------------
+def decode_attention_num_splits(B: int, Hq: int, Hkv: int, D: int, Dv: int, max_seq_len: int, hint: int = 0) -> int:
+    return load().b200_decode_attn_num_splits(B, Hq, Hkv, D, Dv, max_seq_len, hint)
+
+
+def decode_attention_workspace_bytes(B: int, Hq: int, Dv: int, num_splits: int) -> int:
+    return load().b200_decode_attn_workspace_size(B, Hq, Dv, num_splits)
+
+
+def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logits, req_to_token, req_pool_indices,
+                     seq_lens, sm_scale: float, logit_cap: float, *, max_seq_len: int = 0, num_splits: int = 0,
+                     fused_kv_write: bool = False) -> torch.Tensor:
+    """Same positional signature as torch.ops.sgl_kernel.decode_attention_cpu (decode.cpp:1375-1388;
+    schema torch_extension_cpu.cpp:264-268) on CUDA tensors.
+
+    query [B,Hq,D]; k_cache/v_cache [T,Hkv,D]/[T,Hkv,Dv] (last dim contiguous, :1394-1399); output [B,Hq,Dv];
+    key/value [B,Hkv,D]/[B,Hkv,Dv] are written to k_cache[loc]/v_cache[loc] first (None = no write);
+    attn_logits = fp32 scratch (any shape, only its byte size matters; None = allocate).
+    MLA is detected like the reference: k_cache and v_cache share storage, Hkv == 1, D == Dv + 64 (:1455).
+    fused_kv_write=True moves the append into the attention kernel; it requires that slot loc[b] is referenced
+    by request b only (true for SGLang's allocators; schedule_batch.py:1556-1568)."""
+    dev = require_cuda(query, k_cache, v_cache, output, key, value, loc, attn_logits, req_to_token, req_pool_indices,
+                       seq_lens)
+    if query.dim() != 3 or k_cache.dim() != 3 or v_cache.dim() != 3:
+        raise RuntimeError("query, k_cache, v_cache must be 3-d")
+    if query.stride(-1) != 1 or k_cache.stride(-1) != 1 or v_cache.stride(-1) != 1:
+        raise RuntimeError("query, k_cache and v_cache must be contiguous in the last dimension")
+    B, Hq, D = query.shape
+    Hkv, Dv = k_cache.shape[1], v_cache.shape[2]
+    if k_cache.shape[2] != D or v_cache.shape[1] != Hkv:
+        raise RuntimeError("k_cache / v_cache shapes do not match query")
+    if tuple(output.shape) != (B, Hq, Dv) or not output.is_contiguous():
+        raise RuntimeError("output must be a contiguous [B, Hq, Dv] tensor")
+    if not (query.dtype == k_cache.dtype == v_cache.dtype == output.dtype) or query.dtype not in DTYPE_CODE:
+        raise RuntimeError("query, k_cache, v_cache, output must share a bf16/f16 dtype")
+    if req_to_token.dtype not in (torch.int32, torch.int64) or req_to_token.stride(1) != 1:
+        raise RuntimeError("req_to_token must be int32/int64 with contiguous rows")  # decode.cpp:1441-1445
+    for name, t in (("seq_lens", seq_lens), ("req_pool_indices", req_pool_indices)):
+        if t.dtype != torch.int64 or not t.is_contiguous():
+            raise RuntimeError(f"{name} must be a contiguous int64 tensor")  # decode.cpp:1446-1450
+    if seq_lens.numel() != B or req_pool_indices.numel() != B:
+        raise RuntimeError("seq_lens / req_pool_indices must have B entries")
+    write_kv = 0
+    if key is not None:
+        if loc is None or loc.dtype != torch.int64 or not loc.is_contiguous() or loc.numel() != B:
+            raise RuntimeError("loc must be a contiguous int64 [B] tensor")
+        if key.stride(-1) != 1 or (value is not None and value.stride(-1) != 1):
+            raise RuntimeError("key and value must be contiguous in the last dimension")
+        write_kv = 2 if fused_kv_write else 1
+    lib = load()
+    p = _lib.DecodeAttnParams()
+    p.q, p.q_stride_b, p.q_stride_h = query.data_ptr(), query.stride(0), query.stride(1)
+    if key is not None:
+        p.k_new, p.knew_stride_b, p.knew_stride_h = key.data_ptr(), key.stride(0), key.stride(1)
+        v_src = value if value is not None else key
+        p.v_new, p.vnew_stride_b, p.vnew_stride_h = v_src.data_ptr(), v_src.stride(0), v_src.stride(1)
+        p.out_cache_loc = loc.data_ptr()
+    p.k_buf, p.kbuf_stride_t, p.kbuf_stride_h = k_cache.data_ptr(), k_cache.stride(0), k_cache.stride(1)
+    p.v_buf, p.vbuf_stride_t, p.vbuf_stride_h = v_cache.data_ptr(), v_cache.stride(0), v_cache.stride(1)
+    p.out = output.data_ptr()
+    p.req_to_token, p.req_to_token_stride = req_to_token.data_ptr(), req_to_token.stride(0)
+    p.idx_is_i64 = int(req_to_token.dtype == torch.int64)
+    p.req_pool_indices, p.seq_lens = req_pool_indices.data_ptr(), seq_lens.data_ptr()
+    p.B, p.Hq, p.Hkv, p.D, p.Dv = B, Hq, Hkv, D, Dv
+    p.dtype = DTYPE_CODE[query.dtype]
+    p.write_kv = write_kv
+    p.max_seq_len = int(max_seq_len)
+    p.sm_scale, p.logit_cap = float(sm_scale), float(logit_cap)
+    S = lib.b200_decode_attn_num_splits(B, Hq, Hkv, D, Dv, int(max_seq_len), int(num_splits)) if B > 0 else 1
+    p.num_splits = S
+    need = lib.b200_decode_attn_workspace_size(B, Hq, Dv, S)
+    if attn_logits is None or attn_logits.numel() * attn_logits.element_size() < need or not attn_logits.is_contiguous():
+        attn_logits = torch.empty(need, dtype=torch.uint8, device=dev)
+    p.workspace, p.workspace_bytes = attn_logits.data_ptr(), attn_logits.numel() * attn_logits.element_size()
+    with torch.cuda.device(dev):
+        check(lib.b200_decode_attn(p, current_stream(dev)))
+    return output
+
+
+def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices, seq_lens,
+                     extend_seq_lens, extend_start_loc, max_len_extend: int, sm_scale: float, logit_cap: float):
+    """Same positional signature as torch.ops.sgl_kernel.extend_attention_cpu (torch_extension_cpu.cpp:271-275)."""
+    dev = require_cuda(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices,
+                       seq_lens, extend_seq_lens, extend_start_loc)
+    for t in (q_extend, k_extend, v_extend, k_buffer, v_buffer):
+        if t.dim() != 3 or t.stride(-1) != 1:
+            raise RuntimeError("q/k/v tensors must be 3-d and contiguous in the last dimension")
+    T, Hq, D = q_extend.shape
+    Hkv, Dv = k_buffer.shape[1], v_buffer.shape[2]
+    if tuple(o_extend.shape) != (T, Hq, Dv) or not o_extend.is_contiguous():
+        raise RuntimeError("o_extend must be a contiguous [T, Hq, Dv] tensor")
+    rpi, sl, el, es = _i64(req_pool_indices), _i64(seq_lens), _i64(extend_seq_lens), _i64(extend_start_loc)
+    p = _lib.ExtendAttnParams()
+    p.q, p.q_stride_t, p.q_stride_h = q_extend.data_ptr(), q_extend.stride(0), q_extend.stride(1)
+    p.k_ext, p.kext_stride_t, p.kext_stride_h = k_extend.data_ptr(), k_extend.stride(0), k_extend.stride(1)
+    p.v_ext, p.vext_stride_t, p.vext_stride_h = v_extend.data_ptr(), v_extend.stride(0), v_extend.stride(1)
+    p.out = o_extend.data_ptr()
+    p.k_buf, p.kbuf_stride_t, p.kbuf_stride_h = k_buffer.data_ptr(), k_buffer.stride(0), k_buffer.stride(1)
+    p.v_buf, p.vbuf_stride_t, p.vbuf_stride_h = v_buffer.data_ptr(), v_buffer.stride(0), v_buffer.stride(1)
+    p.req_to_token, p.req_to_token_stride = req_to_token.data_ptr(), req_to_token.stride(0)
+    p.idx_is_i64 = int(req_to_token.dtype == torch.int64)
+    p.req_pool_indices, p.seq_lens = rpi.data_ptr(), sl.data_ptr()
+    p.extend_seq_lens, p.extend_start_loc = el.data_ptr(), es.data_ptr()
+    p.B, p.Hq, p.Hkv, p.D, p.Dv = rpi.numel(), Hq, Hkv, D, Dv
+    p.max_len_extend = int(max_len_extend)
+    p.dtype = DTYPE_CODE[q_extend.dtype]
+    p.sm_scale, p.logit_cap = float(sm_scale), float(logit_cap)
+    with torch.cuda.device(dev):
+        check(load().b200_extend_attn(p, current_stream(dev)))
+    return o_extend
+
+
+def set_kv_buffer(k_buffer, v_buffer, loc, cache_k, cache_v) -> None:
+    """KVCache.set_kv_buffer's scatter (memory_pool.py:454-455): k_buffer[loc] = cache_k; v_buffer[loc] = cache_v."""
+    dev = require_cuda(k_buffer, v_buffer, loc, cache_k, cache_v)
+    loc = _i64(loc)
+    B = loc.numel()
+    ck = cache_k.view(B, k_buffer.shape[1], k_buffer.shape[2])
+    cv = cache_v.view(B, v_buffer.shape[1], v_buffer.shape[2]) if cache_v is not None else None
+    with torch.cuda.device(dev):
+        check(load().b200_set_kv_buffer(
+            ptr(k_buffer), k_buffer.stride(0), k_buffer.stride(1), ptr(v_buffer), v_buffer.stride(0), v_buffer.stride(1),
+            ptr(ck), ck.stride(0), ck.stride(1), ptr(cv), cv.stride(0) if cv is not None else 0,
+            cv.stride(1) if cv is not None else 0, ptr(loc), B, k_buffer.shape[1], k_buffer.shape[2], v_buffer.shape[2],
+            k_buffer.element_size(), current_stream(dev)))
+
+
+# ---------------------------------------------------------------------------------------------
+# the steps either side of the path
+# ---------------------------------------------------------------------------------------------
+def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    dev = require_cuda(x, weight, residual)
+    assert x.is_contiguous() and x.dim() == 2
+    out = torch.empty_like(x)
+    with torch.cuda.device(dev):
+        check(load().b200_rmsnorm(ptr(x), ptr(residual), ptr(weight), ptr(out), DTYPE_CODE[x.dtype], x.shape[0], x.shape[1],
+                                  eps, current_stream(dev)))
+    return out
+
+
+def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
+    dev = require_cuda(x)
+    assert x.is_contiguous() and x.dim() == 2
+    d = x.shape[1] // 2
+    out = torch.empty((x.shape[0], d), dtype=x.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(load().b200_silu_and_mul(ptr(x), ptr(out), DTYPE_CODE[x.dtype], x.shape[0], d, current_stream(dev)))
+    return out
+
+
+def rope_neox_(q: torch.Tensor, k: torch.Tensor, positions: torch.Tensor, head_dim: int, theta: float = 10000.0) -> None:
+    dev = require_cuda(q, k, positions)
+    assert q.is_contiguous() and k.is_contiguous() and positions.dtype == torch.int64
+    M = positions.numel()
+    with torch.cuda.device(dev):
+        check(load().b200_rope_neox(ptr(q), ptr(k), ptr(positions), DTYPE_CODE[q.dtype], M, q.numel() // (M * head_dim),
+                                    k.numel() // (M * head_dim), head_dim, theta, current_stream(dev)))

@@ -1,0 +1,225 @@
+/*
+ * b200_sgl.h -- C ABI of the B200-native (sm_100a) decode hot path.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and strides, no torch types.  Each entry
+ * point names the reference interface it replaces (paths relative to the reference tree,
+ * rzwei/iaas-sglang = SGLang 0.4.9 + sgl-kernel 0.2.4).  The Python host code in
+ * iaas_sglang_b200/ (ops.py, backend.py) binds these with ctypes; INTEGRATION.md shows the
+ * reference-side stub.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless it says "host";
+ *   - the caller owns every buffer; nothing here allocates, frees or synchronises;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it and is
+ *     CUDA-graph capturable;
+ *   - strides are in ELEMENTS of the tensor's dtype;
+ *   - return value: 0 = ok, B200_ERR_ARG (-1) = bad argument (-> RuntimeError),
+ *     B200_ERR_UNSUPPORTED (-2) = unsupported shape / device (-> NotImplementedError),
+ *     B200_ERR_CUDA (-3) = CUDA runtime error; b200_last_error() returns the message
+ *     (thread-local, valid until the next failing call on that thread).
+ *   - there is no CPU fallback: on a device that is not sm_100 every compute entry point
+ *     returns B200_ERR_UNSUPPORTED.
+ */
+#ifndef B200_SGL_H_
+#define B200_SGL_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_ARG (-1)
+#define B200_ERR_UNSUPPORTED (-2)
+#define B200_ERR_CUDA (-3)
+
+/* dtype codes */
+#define B200_BF16 0
+#define B200_F16 1
+#define B200_F32 2
+
+#define B200_SGL_ABI_VERSION 1
+
+const char* b200_last_error(void);
+int b200_abi_version(void);
+/* compute capability of the current device as major*10+minor (100 on B200), or a negative error */
+int b200_sm_arch(void);
+int b200_sm_count(void);
+
+/* --------------------------------------------------------------------------------------------
+ * Decode attention over the paged KV pool.
+ *
+ * Replaces, behind AttentionBackend.forward_decode
+ * (python/sglang/srt/layers/attention/base_attn_backend.py:89-99):
+ *   torch.ops.sgl_kernel.decode_attention_cpu   sgl-kernel/csrc/cpu/decode.cpp:1375-1575
+ *                                               (schema csrc/cpu/torch_extension_cpu.cpp:264-268)
+ *   decode_attention_fwd (Triton)               python/sglang/srt/layers/attention/triton_ops/decode_attention.py:677-728
+ *   KVCache.set_kv_buffer                       python/sglang/srt/mem_cache/memory_pool.py:418-456 (fused, write_kv)
+ *
+ *   for b < B:  idx = req_to_token[req_pool_indices[b], 0 : seq_lens[b]]          (read in place)
+ *     if write_kv: k_buf[out_cache_loc[b]] = k_new[b]; v_buf[out_cache_loc[b]] = v_new[b]
+ *     out[b,h,:] = softmax(sm_scale * q[b,h,:] . k_buf[idx, h / (Hq/Hkv), :]  (+ logit_cap tanh)) . v_buf[idx, h / (Hq/Hkv), :]
+ *
+ * MLA (absorbed) decode is the same call with Hkv = 1, D = Dv + 64 and v_buf == k_buf
+ * (v is the first Dv columns of the latent row; decode.cpp:1455, memory_pool.py:829-837).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_decode_attn_params {
+  const void* q;            /* [B, Hq, D]   */
+  int64_t q_stride_b, q_stride_h;
+  const void* k_new;        /* [B, Hkv, D]  new token's key (may be NULL if !write_kv) */
+  int64_t knew_stride_b, knew_stride_h;
+  const void* v_new;        /* [B, Hkv, Dv] */
+  int64_t vnew_stride_b, vnew_stride_h;
+  void* k_buf;              /* [T, Hkv, D]  token_to_kv_pool.get_key_buffer(layer)   */
+  int64_t kbuf_stride_t, kbuf_stride_h;
+  void* v_buf;              /* [T, Hkv, Dv] token_to_kv_pool.get_value_buffer(layer) */
+  int64_t vbuf_stride_t, vbuf_stride_h;
+  void* out;                /* [B, Hq, Dv] contiguous */
+  const void* req_to_token; /* [max_reqs, max_context_len] int32 or int64 */
+  int64_t req_to_token_stride;
+  const int64_t* req_pool_indices; /* [B] */
+  const int64_t* seq_lens;         /* [B] includes the token being decoded */
+  const int64_t* out_cache_loc;    /* [B] */
+  void* workspace;          /* >= b200_decode_attn_workspace_size(...) bytes, 16-byte aligned */
+  size_t workspace_bytes;
+  int32_t idx_is_i64;
+  int32_t B, Hq, Hkv, D, Dv;
+  int32_t dtype;            /* B200_BF16 | B200_F16 (q, k, v, out) */
+  int32_t write_kv;         /* fuse set_kv_buffer */
+  int32_t num_splits;       /* KV splits per request; <= 0: choose from max_seq_len */
+  int32_t max_seq_len;      /* host-side upper bound of seq_lens (e.g. seq_lens_cpu.max()); 0 = unknown */
+  float sm_scale;
+  float logit_cap;          /* 0 = off */
+} b200_decode_attn_params;
+
+/* number of KV splits the kernel will use for this problem (so that the caller can size scratch) */
+int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv, int max_seq_len, int num_splits_hint);
+size_t b200_decode_attn_workspace_size(int B, int Hq, int Dv, int num_splits);
+int b200_decode_attn(const b200_decode_attn_params* p, void* stream);
+
+/* KVCache.set_kv_buffer alone (memory_pool.py:418-456; decode.cpp:771-809): rows scatter, bit-exact */
+int b200_set_kv_buffer(void* k_buf, int64_t kbuf_stride_t, int64_t kbuf_stride_h, void* v_buf, int64_t vbuf_stride_t,
+                       int64_t vbuf_stride_h, const void* k_new, int64_t knew_stride_b, int64_t knew_stride_h,
+                       const void* v_new, int64_t vnew_stride_b, int64_t vnew_stride_h, const int64_t* loc, int B,
+                       int Hkv, int D, int Dv, int elem_bytes, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * Extend (prefill) attention: AttentionBackend.forward_extend (base_attn_backend.py:101-111);
+ * replaces torch.ops.sgl_kernel.extend_attention_cpu (csrc/cpu/extend.cpp; schema
+ * torch_extension_cpu.cpp:271-275) / extend_attention_fwd (triton_ops/extend_attention.py).
+ * Token i of request b (i < extend_seq_lens[b], stored at row extend_start_loc[b] + i) attends to
+ * the request's cached prefix (seq_lens[b] - extend_seq_lens[b] tokens, read through req_to_token
+ * from k_buf/v_buf) and causally to extend tokens 0..i (read from k_ext/v_ext).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_extend_attn_params {
+  const void* q;      /* [T_ext, Hq, D]  */
+  int64_t q_stride_t, q_stride_h;
+  const void* k_ext;  /* [T_ext, Hkv, D] */
+  int64_t kext_stride_t, kext_stride_h;
+  const void* v_ext;  /* [T_ext, Hkv, Dv] */
+  int64_t vext_stride_t, vext_stride_h;
+  void* out;          /* [T_ext, Hq, Dv] contiguous */
+  const void* k_buf;
+  int64_t kbuf_stride_t, kbuf_stride_h;
+  const void* v_buf;
+  int64_t vbuf_stride_t, vbuf_stride_h;
+  const void* req_to_token;
+  int64_t req_to_token_stride;
+  const int64_t* req_pool_indices;  /* [B] */
+  const int64_t* seq_lens;          /* [B] prefix + extend */
+  const int64_t* extend_seq_lens;   /* [B] */
+  const int64_t* extend_start_loc;  /* [B] */
+  int32_t idx_is_i64;
+  int32_t B, Hq, Hkv, D, Dv;
+  int32_t max_len_extend;
+  int32_t dtype;
+  float sm_scale;
+  float logit_cap;
+} b200_extend_attn_params;
+int b200_extend_attn(const b200_extend_attn_params* p, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * Page-table index builders (integer, bit-exact), python/sglang/srt/layers/attention/utils.py
+ * ------------------------------------------------------------------------------------------ */
+/* create_flashinfer_kv_indices_triton (utils.py:5-41):
+ *   kv_indices[kv_indptr[b] + j] = req_to_token[req_pool_indices[b], kv_start[b] + j], j < lens[b] */
+int b200_create_kv_indices(const void* req_to_token, int idx_is_i64, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* lens, const int64_t* kv_indptr,
+                           const int64_t* kv_start /* NULL = 0 */, int32_t* kv_indices, int B, void* stream);
+/* create_flashmla_kv_indices_triton (utils.py:44-94): out[b,p] = req_to_token[req, start + p*P] / P */
+int b200_create_page_table(const void* req_to_token, int idx_is_i64, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* lens, const int64_t* kv_start,
+                           int32_t* out, int64_t out_stride, int B, int page_size, int max_pages, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * Activation quantisation
+ * ------------------------------------------------------------------------------------------ */
+/* sgl_per_token_group_quant_fp8 (sgl-kernel/csrc/gemm/per_token_group_quant_8bit.cu:25-115,230-240;
+ * schema common_extension.cc:116-119):  absmax = max(eps, max|x|) over each group of `group`
+ * columns; s = absmax / fp8_max; q = e4m3(clamp(x / s)).  s[m, g] is stored at s[m*s_stride_m + g*s_stride_g]
+ * (column_major_scales=True -> s_stride_m = 1). */
+int b200_per_token_group_quant_fp8(const void* x, int64_t x_stride_m, int x_dtype, void* q, int64_t q_stride_m,
+                                   float* s, int64_t s_stride_m, int64_t s_stride_g, int M, int K, int group,
+                                   float eps, float fp8_min, float fp8_max, void* stream);
+/* per_token_quant_int8 (python/sglang/srt/layers/quantization/int8_kernel.py:20-81):
+ * absmax = max(max|x|, 1e-10); s[m] = absmax/127; q = round_half_away(x * (127/absmax)) */
+int b200_per_token_quant_int8(const void* x, int64_t x_stride_m, int x_dtype, int8_t* q, int64_t q_stride_m, float* s,
+                              int M, int K, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * Quantised GEMMs (tcgen05 + TMEM + TMA)
+ * ------------------------------------------------------------------------------------------ */
+/* fp8_blockwise_scaled_mm (sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:345-423; schema
+ * common_extension.cc:111-114; python sgl_kernel/gemm.py:24-31):
+ *   out[m,n] = sum_kb sa[m,kb] * sb[kb,nb] * sum_{k in block kb} a[m,k] * b[k,n]      (128x128 blocks)
+ * a: [M,K] e4m3 row-major (lda elements); b: [K,N] COLUMN-major, i.e. the [N,K] row-major weight
+ * (ldb = elements between consecutive n); sa: [M, ceil(K/128)] f32 at sa[m*sa_stride_m + kb*sa_stride_k]
+ * (reference requires M-major: sa_stride_m == 1); sb: [ceil(K/128), ceil(N/128)] f32 at
+ * sb[kb*sb_stride_k + nb*sb_stride_n]; out: [M,N] row-major bf16/f16 (ldo elements). */
+/* split-K scratch for the two GEMMs below: `workspace` must be zero-filled ONCE before its first use
+ * (it holds self-resetting tile tickets) and must not be shared by GEMMs running concurrently. */
+size_t b200_gemm_workspace_size(int M, int N, int K);
+int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
+                                 int64_t sa_stride_m, int64_t sa_stride_k, const float* sb, int64_t sb_stride_k,
+                                 int64_t sb_stride_n, void* out, int64_t ldo, int out_dtype, int M, int N, int K,
+                                 void* workspace, size_t workspace_bytes, void* stream);
+/* int8_scaled_mm (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747; schema common_extension.cc:101-104):
+ *   out[m,n] = ((float)(sum_k a[m,k]*b[k,n]) * sa[m]) * sb[n] + bias[n]
+ * a: [M,K] int8 row-major; b: [K,N] column-major; bias: [N] of out dtype or NULL. */
+int b200_int8_scaled_mm(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa, const float* sb,
+                        const void* bias, void* out, int64_t ldo, int out_dtype, int M, int N, int K, void* workspace,
+                        size_t workspace_bytes, void* stream);
+/* awq_dequantize (sgl-kernel/csrc/gemm/awq_kernel.cu:126-221; schema common_extension.cc:98-99):
+ *   out[r, 8c+j] = half((nib(qweight[r,c], ord[j]) - nib(qzeros[r/g,c], ord[j])) * scales[r/g, 8c+j]),
+ *   ord = {0,4,1,5,2,6,3,7}.  qweight [rows, cols] int32, qzeros [rows/g, cols], scales [rows/g, 8*cols]. */
+int b200_awq_dequantize(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int dtype,
+                        int rows, int cols, int group, void* stream);
+/* AWQLinearMethod.apply (python/sglang/srt/layers/quantization/awq.py:186-204):
+ *   out[M,N] = x[M,K] @ dequant(qweight[K,N/8], scales, qzeros) (+ bias).
+ * v1 stages the dequantised weight K-major in `workspace` (>= b200_awq_w4a16_workspace_size bytes,
+ * 256-byte aligned, zero-filled once) and runs the tcgen05 half-precision GEMM on it. */
+size_t b200_awq_w4a16_workspace_size(int M, int N, int K);
+int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qweight, const void* scales, const int32_t* qzeros,
+                      const void* bias, void* out, int64_t ldo, int dtype, int M, int N, int K, int group,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* --------------------------------------------------------------------------------------------
+ * The steps either side of the path, used by the decode-step harness:
+ * RMSNorm (+residual add), SiLU-and-mul, neox RoPE.  References:
+ *   sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu, python/sglang/srt/layers/layernorm.py,
+ *   sgl-kernel/csrc/elementwise/activation.cu, python/sglang/srt/layers/rotary_embedding.py
+ * ------------------------------------------------------------------------------------------ */
+/* if residual != NULL: residual += x (stored back, half precision), then out = rmsnorm(residual)*w */
+int b200_rmsnorm(const void* x, void* residual, const void* weight, void* out, int dtype, int M, int H, float eps,
+                 void* stream);
+int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int d, void* stream);
+/* in-place neox-style rotary embedding on q [M,Hq,D] and k [M,Hkv,D] (contiguous), positions int64 [M] */
+int b200_rope_neox(void* q, void* k, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D, float theta,
+                   void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_SGL_H_ */

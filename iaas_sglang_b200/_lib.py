@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200_abi_version": (c_int, []),
     "b200_sm_arch": (c_int, []),
     "b200_sm_count": (c_int, []),
+    "b200_launch_count": (C.c_ulonglong, []),
     "b200_decode_attn_num_splits": (c_int, [c_int] * 7),
     "b200_decode_attn_workspace_size": (c_size_t, [c_int] * 4),
     "b200_decode_attn": (c_int, [C.POINTER(DecodeAttnParams), c_void_p]),

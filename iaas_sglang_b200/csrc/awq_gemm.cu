@@ -81,7 +81,7 @@ extern "C" int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qwei
     awq_dequant_t_kernel<true><<<grid, 256, 0, st>>>(qweight, (const uint16_t*)scales, qzeros, wt, K, cols, group);
   else
     awq_dequant_t_kernel<false><<<grid, 256, 0, st>>>(qweight, (const uint16_t*)scales, qzeros, wt, K, cols, group);
-  if (int rc = check_cuda(cudaGetLastError(), "awq_dequant_t_kernel launch")) return rc;
+  if (int rc = launched("awq_dequant_t_kernel launch")) return rc;
   return dense_half_gemm(x, ldx, wt, K, bias, out, ldo, dtype, M, N, K, gemm_ws_ptr, gemm_ws, st);
 }
 

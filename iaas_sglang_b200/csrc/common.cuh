@@ -17,6 +17,8 @@ namespace b200 {
 // ---------------------------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
+// call right after a <<<>>> launch: counts it (b200_launch_count) and returns the launch status
+int launched(const char* what);
 int device_sm_count();
 
 #define B200_REQUIRE(cond, code, ...)  \

@@ -243,7 +243,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       alpha[r] = exp2f(m_run[r] - m_use[r]);
       m_run[r] = m_new;
     }
-    uint32_t pa[4];
+    // P is split into hi + lo half-precision parts (p = hi + lo up to 2^-17) and PV is issued twice,
+    // so the result matches an fp32-P reference (decode.cpp:972-984 keeps P in fp32 for MHA/GQA);
+    // the extra MMAs are free for an HBM-bound kernel.
+    uint32_t pa[4], pb[4];
     float ps[2] = {0.f, 0.f};
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
@@ -251,10 +254,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       const float p2 = exp2f(sc[nt][2] - m_use[1]), p3 = exp2f(sc[nt][3] - m_use[1]);
       pa[nt * 2 + 0] = pack_half2<BF16>(p0, p1);
       pa[nt * 2 + 1] = pack_half2<BF16>(p2, p3);
-      // sum the ROUNDED probabilities so numerator and denominator use the same weights
-      const float2 f01 = unpack_half2<BF16>(pa[nt * 2 + 0]), f23 = unpack_half2<BF16>(pa[nt * 2 + 1]);
-      ps[0] += f01.x + f01.y;
-      ps[1] += f23.x + f23.y;
+      const float2 h01 = unpack_half2<BF16>(pa[nt * 2 + 0]), h23 = unpack_half2<BF16>(pa[nt * 2 + 1]);
+      pb[nt * 2 + 0] = pack_half2<BF16>(p0 - h01.x, p1 - h01.y);
+      pb[nt * 2 + 1] = pack_half2<BF16>(p2 - h23.x, p3 - h23.y);
+      ps[0] += p0 + p1;
+      ps[1] += p2 + p3;
     }
     l_run[0] = l_run[0] * alpha[0] + ps[0];
     l_run[1] = l_run[1] * alpha[1] + ps[1];
@@ -273,6 +277,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       ldsm_x4_t(vbase + v_lane_off + jp * 32, r0, r1, r2, r3);
       mma_16816<BF16>(o[2 * jp], pa, r0, r1);
       mma_16816<BF16>(o[2 * jp + 1], pa, r2, r3);
+      mma_16816<BF16>(o[2 * jp], pb, r0, r1);
+      mma_16816<BF16>(o[2 * jp + 1], pb, r2, r3);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);
@@ -394,7 +400,7 @@ __global__ void __launch_bounds__(128) decode_attn_generic_kernel(const __grid_c
     const float alpha = exp2f(m_run - m_new);
     float pr = exp2f(s - m_new);
     l_run = l_run * alpha + pr;
-    if (p.is_mla) pr = half_to_float<BF16>(float_to_half<BF16>(pr));  // decode.cpp:1157-1159
+    // (the reference's MLA path rounds pr to bf16 here, decode.cpp:1157-1159; we keep fp32 -- see DESIGN.md)
     m_run = m_new;
 #pragma unroll
     for (int e = 0; e < MAXE; ++e) {
@@ -519,7 +525,7 @@ static int launch_mma(const DecodeKParams& kp, cudaStream_t st) {
   const int n_qblk = (kp.G + 15) / 16;
   dim3 grid(kp.num_splits, (kp.Hkv / HPC) * n_qblk, kp.B);
   kern<<<grid, kAttnThreads, C::SMEM_BYTES, st>>>(kp);
-  return check_cuda(cudaGetLastError(), "decode_attn_mma_kernel launch");
+  return launched("decode_attn_mma_kernel launch");
 }
 
 template <bool BF16>
@@ -541,7 +547,7 @@ static int launch_generic(const DecodeKParams& kp, cudaStream_t st) {
   else if (mx <= 256) decode_attn_generic_kernel<8, BF16><<<grid, 128, 0, st>>>(kp);
   else if (mx <= 640) decode_attn_generic_kernel<20, BF16><<<grid, 128, 0, st>>>(kp);
   else decode_attn_generic_kernel<32, BF16><<<grid, 128, 0, st>>>(kp);
-  return check_cuda(cudaGetLastError(), "decode_attn_generic_kernel launch");
+  return launched("decode_attn_generic_kernel launch");
 }
 
 }  // namespace b200
@@ -584,7 +590,7 @@ extern "C" int b200_set_kv_buffer(void* k_buf, int64_t kb_st, int64_t kb_sh, voi
   set_kv_kernel<<<dim3(B, Hkv), 128, 0, (cudaStream_t)stream>>>(
       (uint16_t*)k_buf, kb_st, kb_sh, (uint16_t*)v_buf, vb_st, vb_sh, (const uint16_t*)k_new, kn_sb, kn_sh,
       (const uint16_t*)v_new, vn_sb, vn_sh, loc, D, Dv);
-  return check_cuda(cudaGetLastError(), "set_kv_kernel launch");
+  return launched("set_kv_kernel launch");
 }
 
 extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) {
@@ -672,7 +678,7 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
       decode_merge_kernel<true><<<a->B * a->Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, S, a->Dv);
     else
       decode_merge_kernel<false><<<a->B * a->Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, S, a->Dv);
-    return check_cuda(cudaGetLastError(), "decode_merge_kernel launch");
+    return launched("decode_merge_kernel launch");
   }
   return B200_OK;
 }

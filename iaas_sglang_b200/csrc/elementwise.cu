@@ -244,7 +244,7 @@ extern "C" int b200_create_kv_indices(const void* r2t, int idx64, int64_t r2t_st
   if (B == 0) return B200_OK;
   if (int rc = require_sm100("create_kv_indices")) return rc;
   kv_indices_kernel<<<dim3(B, 8), 512, 0, (cudaStream_t)stream>>>(r2t, idx64, r2t_stride, rpi, lens, indptr, kv_start, out);
-  return check_cuda(cudaGetLastError(), "kv_indices_kernel launch");
+  return launched("kv_indices_kernel launch");
 }
 
 extern "C" int b200_create_page_table(const void* r2t, int idx64, int64_t r2t_stride, const int64_t* rpi,
@@ -255,7 +255,7 @@ extern "C" int b200_create_page_table(const void* r2t, int idx64, int64_t r2t_st
   if (int rc = require_sm100("create_page_table")) return rc;
   page_table_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(r2t, idx64, r2t_stride, rpi, lens, kv_start, out, out_stride,
                                                         page_size, max_pages);
-  return check_cuda(cudaGetLastError(), "page_table_kernel launch");
+  return launched("page_table_kernel launch");
 }
 
 extern "C" int b200_per_token_group_quant_fp8(const void* x, int64_t x_sm, int x_dtype, void* q, int64_t q_sm, float* s,
@@ -283,7 +283,7 @@ extern "C" int b200_per_token_group_quant_fp8(const void* x, int64_t x_sm, int x
     else
       group_quant_fp8_generic_kernel<false><<<blocks, 256, 0, st>>>((const uint16_t*)x, x_sm, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, gpr, group, eps, fp8_min, fp8_max);
   }
-  return check_cuda(cudaGetLastError(), "group_quant_fp8_kernel launch");
+  return launched("group_quant_fp8_kernel launch");
 }
 
 extern "C" int b200_per_token_quant_int8(const void* x, int64_t x_sm, int x_dtype, int8_t* q, int64_t q_sm, float* s, int M,
@@ -296,7 +296,7 @@ extern "C" int b200_per_token_quant_int8(const void* x, int64_t x_sm, int x_dtyp
     token_quant_int8_kernel<true><<<M, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, x_sm, q, q_sm, s, K);
   else
     token_quant_int8_kernel<false><<<M, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, x_sm, q, q_sm, s, K);
-  return check_cuda(cudaGetLastError(), "token_quant_int8_kernel launch");
+  return launched("token_quant_int8_kernel launch");
 }
 
 extern "C" int b200_awq_dequantize(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* out, int dtype,
@@ -311,7 +311,7 @@ extern "C" int b200_awq_dequantize(const int32_t* qweight, const void* scales, c
     awq_dequant_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(qweight, (const uint16_t*)scales, qzeros, (uint16_t*)out, rows, cols, group);
   else
     awq_dequant_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(qweight, (const uint16_t*)scales, qzeros, (uint16_t*)out, rows, cols, group);
-  return check_cuda(cudaGetLastError(), "awq_dequant_kernel launch");
+  return launched("awq_dequant_kernel launch");
 }
 
 extern "C" int b200_rmsnorm(const void* x, void* residual, const void* weight, void* out, int dtype, int M, int H, float eps,
@@ -330,7 +330,7 @@ extern "C" int b200_rmsnorm(const void* x, void* residual, const void* weight, v
     rmsnorm_kernel<true><<<M, 256, H * 4, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, (uint16_t*)out, H, eps);
   else
     rmsnorm_kernel<false><<<M, 256, H * 4, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, (uint16_t*)out, H, eps);
-  return check_cuda(cudaGetLastError(), "rmsnorm_kernel launch");
+  return launched("rmsnorm_kernel launch");
 }
 
 extern "C" int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int d, void* stream) {
@@ -344,7 +344,7 @@ extern "C" int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int
     silu_mul_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)out, M, d);
   else
     silu_mul_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)out, M, d);
-  return check_cuda(cudaGetLastError(), "silu_mul_kernel launch");
+  return launched("silu_mul_kernel launch");
 }
 
 extern "C" int b200_rope_neox(void* q, void* k, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D,
@@ -357,5 +357,5 @@ extern "C" int b200_rope_neox(void* q, void* k, const int64_t* positions, int dt
     rope_neox_kernel<true><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, (uint16_t*)k, positions, Hq, Hkv, D, log2f(theta));
   else
     rope_neox_kernel<false><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, (uint16_t*)k, positions, Hq, Hkv, D, log2f(theta));
-  return check_cuda(cudaGetLastError(), "rope_neox_kernel launch");
+  return launched("rope_neox_kernel launch");
 }

@@ -112,7 +112,7 @@ static int launch_extend(const ExtendKParams& kp, dim3 grid, cudaStream_t st) {
   else if (mx <= 256) extend_attn_kernel<8, BF16><<<grid, 128, 0, st>>>(kp);
   else if (mx <= 640) extend_attn_kernel<20, BF16><<<grid, 128, 0, st>>>(kp);
   else extend_attn_kernel<32, BF16><<<grid, 128, 0, st>>>(kp);
-  return check_cuda(cudaGetLastError(), "extend_attn_kernel launch");
+  return launched("extend_attn_kernel launch");
 }
 
 }  // namespace b200

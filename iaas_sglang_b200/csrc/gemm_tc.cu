@@ -335,7 +335,7 @@ static int launch_gemm(const void* a, int64_t lda, const void* b, int64_t ldb, G
   }
   dim3 grid(sp.tiles_n, sp.tiles_m, sp.splits);
   kern<<<grid, kGemmThreads, kGemmSmem, st>>>(ta, tb, gp);
-  return check_cuda(cudaGetLastError(), "gemm_tc_kernel launch");
+  return launched("gemm_tc_kernel launch");
 }
 
 }  // namespace b200

@@ -22,6 +22,14 @@ int check_cuda(cudaError_t e, const char* what) {
   return B200_ERR_CUDA;
 }
 
+static unsigned long long g_launches = 0;
+
+int launched(const char* what) {
+  __atomic_add_fetch(&g_launches, 1ULL, __ATOMIC_RELAXED);
+  return check_cuda(cudaGetLastError(), what);
+}
+unsigned long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 int device_sm_count() {
   static int cached[64] = {0};
   int dev = 0;
@@ -90,3 +98,5 @@ extern "C" int b200_sm_arch(void) {
 }
 
 extern "C" int b200_sm_count(void) { return b200::device_sm_count(); }
+namespace b200 { unsigned long long launch_count(); }
+extern "C" unsigned long long b200_launch_count(void) { return b200::launch_count(); }

@@ -47,6 +47,8 @@ int b200_abi_version(void);
 /* compute capability of the current device as major*10+minor (100 on B200), or a negative error */
 int b200_sm_arch(void);
 int b200_sm_count(void);
+/* number of kernels this library has launched (or captured into a CUDA graph) in this process */
+unsigned long long b200_launch_count(void);
 
 /* --------------------------------------------------------------------------------------------
  * Decode attention over the paged KV pool.

@@ -1,0 +1,194 @@
+"""GPU tier: quantised linears (fp8_blockwise_scaled_mm, int8_scaled_mm, awq_dequantize / W4A16 GEMM) and the
+activation quantisers against the CPU oracle and the reference's golden outputs.  Tolerance (north_star):
+quantised GEMM within 1e-2; integer paths (int32 accumulation, nibble extraction, fp8 codes) bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cpu_oracle as orc
+from tests.util import bf16, f16, fp8, golden, make_fp8_gemm_case, max_abs, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def _col_major(t):  # [K,N] view with stride(0) == 1 on the device
+    return t.t().contiguous().cuda().t()
+
+
+def _run_fp8(a, b, sa, sb, dtype=torch.bfloat16):
+    from iaas_sglang_b200 import ops
+
+    out = ops.fp8_blockwise_scaled_mm(a.cuda(), _col_major(b), _col_major(sa), _col_major(sb), dtype)
+    torch.cuda.synchronize()
+    return out.cpu()
+
+
+def test_fp8_blockwise_against_reference_golden():
+    g = golden("quant_gemm")
+    for i in range(int(g["fp8_n"])):
+        p = f"fp8_{i}_"
+        a, w = fp8(g[p + "a"]), fp8(g[p + "w"])
+        sa, sb = torch.from_numpy(g[p + "sa"]), torch.from_numpy(g[p + "sb"])
+        out = _run_fp8(a, w.t(), sa, sb)
+        ref = bf16(g[p + "o"])
+        assert rel_l2(out, ref) < 1e-2
+        torch.testing.assert_close(out.float(), ref.float(), rtol=0.02, atol=1)  # test_fp8_blockwise_gemm.py:80-82
+
+
+FP8_SHAPES = [(1, 128, 512), (3, 512, 1024), (5, 1024, 4096), (127, 512, 512), (128, 4096, 512), (512, 1024, 1024),
+              (64, 6144, 4096), (64, 4096, 4096), (64, 4096, 14336), (256, 1280, 8192), (256, 8192, 1024),
+              (300, 384, 640), (16, 14080, 512), (1024, 2048, 2048)]
+
+
+@pytest.mark.parametrize("M,N,K", FP8_SHAPES)
+@pytest.mark.parametrize("dist", ["uniform448", "realistic"])
+def test_fp8_blockwise_against_oracle(M, N, K, dist):
+    if dist == "realistic" and M * N * K > 64 * 6144 * 4096:
+        pytest.skip("one distribution is enough for the largest shapes")
+    a, b, sa, sb = make_fp8_gemm_case(M, N, K, seed=M + N + K, dist=dist)
+    ref = orc.fp8_blockwise_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    out = _run_fp8(a, b, sa, sb)
+    assert rel_l2(out, ref) < 1e-2, rel_l2(out, ref)
+    assert rel_l2(out, ref) < 1e-3  # in practice: fp32 promotion per 128-block, bf16 output rounding only
+
+
+def test_fp8_blockwise_fp16_out_and_preconditions():
+    from iaas_sglang_b200 import ops
+
+    a, b, sa, sb = make_fp8_gemm_case(33, 256, 512, seed=3, dist="realistic")
+    ref = orc.fp8_blockwise_scaled_mm(a, b, sa, sb, torch.float16)
+    assert rel_l2(_run_fp8(a, b, sa, sb, torch.float16), ref) < 1e-3
+    ad, bd, sad, sbd = a.cuda(), _col_major(b), _col_major(sa), _col_major(sb)
+    with pytest.raises(RuntimeError, match="column major"):
+        ops.fp8_blockwise_scaled_mm(ad, bd.contiguous(), sad, sbd, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="M major"):
+        ops.fp8_blockwise_scaled_mm(ad, bd, sad.contiguous(), sbd, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="Half or BFloat16"):
+        ops.fp8_blockwise_scaled_mm(ad, bd, sad, sbd, torch.float32)
+    assert ops.fp8_blockwise_scaled_mm(ad[:0], bd, sad[:0], sbd, torch.bfloat16).shape == (0, 256)
+
+
+def test_fp8_linearity_property_large():
+    """Size-independent property at a prefill-size GEMM: scaling sa by 2 doubles the output bit-exactly; a sampled
+    set of rows matches the oracle."""
+    M, N, K = 4096, 4096, 4096
+    a, b, sa, sb = make_fp8_gemm_case(M, N, K, seed=11, dist="realistic")
+    out = _run_fp8(a, b, sa, sb)
+    out2 = _run_fp8(a, b, sa * 2, sb)
+    assert torch.equal(out2, out * 2)
+    rows = torch.tensor([0, 1, 127, 128, 2049, 4095])
+    ref = orc.fp8_blockwise_scaled_mm(a[rows], b, sa[rows].t().contiguous().t(), sb, torch.bfloat16)
+    assert rel_l2(out[rows], ref) < 1e-3
+
+
+def test_per_token_group_quant_fp8_bit_exact():
+    from iaas_sglang_b200 import ops
+
+    g = golden("quant_gemm")
+    x = bf16(g["gq_x"])
+    q, s = ops.per_token_group_quant_fp8(x.cuda(), 128)
+    nz = x.view(7, 4, 128).abs().amax(-1) != 0
+    assert torch.equal(s.cpu()[nz], torch.from_numpy(g["gq_s"])[nz])
+    assert np.array_equal(q.cpu().view(torch.uint8).numpy(), g["gq_q"])
+    for M, K, dt in [(64, 4096, torch.bfloat16), (1, 128, torch.float16), (255, 14336, torch.bfloat16), (3, 7168, torch.bfloat16)]:
+        x = (torch.randn(M, K) * 3).to(dt)
+        q0, s0 = orc.per_token_group_quant_fp8(x)
+        for col_major in (True, False):
+            q1, s1 = ops.per_token_group_quant_fp8(x.cuda(), 128, column_major_scales=col_major)
+            assert s1.stride(0) == (1 if col_major and M > 1 else s1.stride(0))
+            assert torch.equal(q0.view(torch.uint8), q1.cpu().view(torch.uint8)) and torch.equal(s0, s1.cpu())
+
+
+def test_per_token_quant_int8_bit_exact():
+    from iaas_sglang_b200 import ops
+
+    for M, K in [(9, 384), (64, 4096), (1, 16), (130, 5120)]:
+        x = (torch.randn(M, K) * 2).to(torch.bfloat16)
+        q0, s0 = orc.per_token_quant_int8(x)
+        q1, s1 = ops.per_token_quant_int8(x.cuda())
+        assert torch.equal(q0, q1.cpu()) and torch.equal(s0, s1.cpu())
+
+
+INT8_SHAPES = [(1, 16, 512), (16, 128, 512), (32, 136, 1024), (130, 256, 512), (64, 4096, 4096), (64, 6144, 4096),
+               (512, 1024, 8192), (300, 136, 1024), (1024, 4096, 512)]
+
+
+@pytest.mark.parametrize("M,N,K", INT8_SHAPES)
+@pytest.mark.parametrize("with_bias", [True, False])
+def test_int8_scaled_mm_bit_exact(M, N, K, with_bias):
+    """test_int8_gemm.py:19-30 inputs; int32 accumulation is exact and the epilogue applies the scales in the
+    reference's order, so the bf16 output equals the oracle bit for bit."""
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(M * 7 + N + K)
+    a = (torch.randn(M, K, generator=g) * 5).clamp(-128, 127).round().to(torch.int8)
+    w = (torch.randn(N, K, generator=g) * 5).clamp(-128, 127).round().to(torch.int8)
+    sa, sb = torch.randn(M, generator=g), torch.randn(N, generator=g)
+    bias = (torch.randn(N, generator=g) * 10).to(torch.bfloat16) if with_bias else None
+    ref = orc.int8_scaled_mm(a, w.t(), sa, sb, torch.bfloat16, bias)
+    out = ops.int8_scaled_mm(a.cuda(), w.cuda().t(), sa.cuda(), sb.cuda(), torch.bfloat16, bias.cuda() if with_bias else None)
+    assert torch.equal(out.cpu(), ref), max_abs(out, ref)
+
+
+def test_int8_against_reference_golden_and_extremes():
+    from iaas_sglang_b200 import ops
+
+    g = golden("quant_gemm")
+    for i in range(int(g["i8_n"])):
+        p = f"i8_{i}_"
+        a, w = torch.from_numpy(g[p + "a"]), torch.from_numpy(g[p + "w"])
+        bias = bf16(g[p + "bias"]).cuda() if p + "bias" in g.files else None
+        out = ops.int8_scaled_mm(a.cuda(), w.cuda().t(), torch.from_numpy(g[p + "sa"]).cuda(),
+                                 torch.from_numpy(g[p + "sb"]).cuda(), torch.bfloat16, bias)
+        assert torch.equal(out.cpu(), bf16(g[p + "o"]))
+    # saturating inputs: -128 * -128 * K stays inside int32 for K = 16384
+    a = torch.full((4, 16384), -128, dtype=torch.int8)
+    w = torch.full((16, 16384), -128, dtype=torch.int8)
+    one_m, one_n = torch.ones(4), torch.ones(16)
+    out = ops.int8_scaled_mm(a.cuda(), w.cuda().t(), one_m.cuda(), one_n.cuda(), torch.bfloat16)
+    assert torch.equal(out.cpu(), orc.int8_scaled_mm(a, w.t(), one_m, one_n, torch.bfloat16))
+
+
+@pytest.mark.parametrize("K,C,dt", [(256, 16, torch.float16), (384, 72, torch.bfloat16), (3584, 448, torch.bfloat16),
+                                    (5120, 448, torch.float16), (128, 32, torch.bfloat16)])
+def test_awq_dequantize_bit_exact(K, C, dt):
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(K + C)
+    qw = torch.randint(0, 2 ** 31 - 1, (K, C), generator=g, dtype=torch.int32)
+    qz = torch.randint(0, 2 ** 31 - 1, (K // 128, C), generator=g, dtype=torch.int32)
+    sc = torch.rand(K // 128, C * 8, generator=g).to(dt)
+    ref = orc.awq_dequantize(qw, sc, qz)
+    out = ops.awq_dequantize(qw.cuda(), sc.cuda(), qz.cuda())
+    assert torch.equal(out.cpu().view(torch.int16), ref.view(torch.int16))
+
+
+def test_awq_dequantize_reference_golden():
+    from iaas_sglang_b200 import ops
+
+    g = golden("quant_gemm")
+    for i in range(int(g["awq_n"])):
+        p = f"awq_{i}_"
+        is_bf16 = bool(g[p + "bf16"])
+        sc = bf16(g[p + "sc"]) if is_bf16 else f16(g[p + "sc"])
+        out = ops.awq_dequantize(torch.from_numpy(g[p + "qw"]).cuda(), sc.cuda(), torch.from_numpy(g[p + "qz"]).cuda())
+        ref = bf16(g[p + "o"]) if is_bf16 else f16(g[p + "o"])
+        assert torch.equal(out.cpu().view(torch.int16), ref.view(torch.int16))
+
+
+@pytest.mark.parametrize("M,K,N,dt", [(16, 512, 1024, torch.bfloat16), (64, 1024, 512, torch.float16),
+                                      (128, 5120, 3584, torch.bfloat16), (1, 2560, 5120, torch.bfloat16),
+                                      (130, 1024, 1088, torch.float16)])
+def test_awq_w4a16_gemm(M, K, N, dt):
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(M + K + N)
+    qw = torch.randint(0, 2 ** 31 - 1, (K, N // 8), generator=g, dtype=torch.int32)
+    qz = torch.randint(0, 2 ** 31 - 1, (K // 128, N // 8), generator=g, dtype=torch.int32)
+    sc = (torch.rand(K // 128, N, generator=g) * 0.01).to(dt)
+    x = torch.randn(M, K, generator=g).to(dt)
+    bias = torch.randn(N, generator=g).to(dt) if M % 2 == 0 else None
+    ref = orc.awq_gemm(x, qw, sc, qz, bias)
+    out = ops.awq_w4a16_gemm(x.cuda(), qw.cuda(), sc.cuda(), qz.cuda(), bias.cuda() if bias is not None else None)
+    assert rel_l2(out, ref) < 1e-2
+    assert rel_l2(out, ref) < 2e-3

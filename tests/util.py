@@ -128,3 +128,67 @@ def make_fp8_gemm_case(M, N, K, seed=0, out_dtype=torch.bfloat16, dist="uniform4
     sa = sa.t().contiguous().t()
     sb = sb.t().contiguous().t()
     return a, b, sa, sb
+
+
+# ---------------------------------------------------------------------------------------------
+# golden fixtures (tests/golden/*.npz, written by tests/golden/make_golden.py from the reference itself)
+# ---------------------------------------------------------------------------------------------
+import os as _os
+
+import numpy as _np
+
+GOLDEN_DIR = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden")
+
+
+def golden(name: str):
+    return _np.load(_os.path.join(GOLDEN_DIR, name + ".npz"))
+
+
+def bf16(a) -> torch.Tensor:
+    return torch.from_numpy(_np.ascontiguousarray(a).view(_np.int16)).view(torch.bfloat16)
+
+
+def f16(a) -> torch.Tensor:
+    return torch.from_numpy(_np.ascontiguousarray(a).view(_np.int16)).view(torch.float16)
+
+
+def fp8(a) -> torch.Tensor:
+    return torch.from_numpy(_np.ascontiguousarray(a)).view(torch.float8_e4m3fn)
+
+
+def golden_decode_cases():
+    """Yield dicts of CPU tensors for every case of tests/golden/decode_attention_cpu.npz."""
+    g = golden("decode_attention_cpu")
+    for i in range(int(g["n_cases"])):
+        p = f"c{i}_"
+        B, Hq, Hkv, D, Dv, S, mla = [int(v) for v in g[p + "shape"]]
+        k_buf = bf16(g[p + "k_buf"])
+        key = bf16(g[p + "key"])
+        c = dict(idx=i, B=B, Hq=Hq, Hkv=Hkv, D=D, Dv=Dv, S=S, mla=bool(mla), cap=float(g[p + "cap"]), q=bf16(g[p + "q"]),
+                 k_buf=k_buf, key=key, r2t=torch.from_numpy(g[p + "r2t"]), seq_lens=torch.from_numpy(g[p + "seq_lens"]),
+                 loc=torch.from_numpy(g[p + "loc"]), o=bf16(g[p + "o"]), rpi=torch.arange(B, dtype=torch.int64))
+        if mla:
+            c["v_buf"], c["value"] = k_buf.narrow(2, 0, Dv), key.narrow(2, 0, Dv)
+        else:
+            c["v_buf"], c["value"] = bf16(g[p + "v_buf"]), bf16(g[p + "value"])
+        yield c
+
+
+def golden_extend_cases():
+    g = golden("extend_attention_cpu")
+    for i in range(int(g["n_cases"])):
+        p = f"c{i}_"
+        B, Hq, Hkv, D, Dv = [int(v) for v in g[p + "shape"]]
+        k_buf, v_buf = bf16(g[p + "k_buf"]), bf16(g[p + "v_buf"])
+        r2t = torch.from_numpy(g[p + "r2t"])
+        sl, el, es = (torch.from_numpy(g[p + n]) for n in ("seq_lens", "ext_lens", "ext_start"))
+        Te = int(el.sum())
+        k_ext = torch.empty(Te, Hkv, D, dtype=torch.bfloat16)
+        v_ext = torch.empty(Te, Hkv, Dv, dtype=torch.bfloat16)
+        for b in range(B):
+            slots = r2t[b, int(sl[b] - el[b]): int(sl[b])].long()
+            k_ext[int(es[b]): int(es[b] + el[b])] = k_buf[slots]
+            v_ext[int(es[b]): int(es[b] + el[b])] = v_buf[slots]
+        yield dict(idx=i, B=B, Hq=Hq, Hkv=Hkv, D=D, Dv=Dv, q=bf16(g[p + "q"]), k_buf=k_buf, v_buf=v_buf, k_ext=k_ext,
+                   v_ext=v_ext, r2t=r2t, seq_lens=sl, ext_lens=el, ext_start=es, rpi=torch.arange(B, dtype=torch.int64),
+                   o=bf16(g[p + "o"]))

@@ -1,0 +1,593 @@
+#!/usr/bin/env python
+"""bench.py -- decode-step throughput of the hot path (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg1|cfg3|cfg4|cfg5]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+One "step" = one decode step of the whole layer stack for one batch: per layer RMSNorm(+residual) -> qkv linear ->
+RoPE -> paged decode attention (fused KV append, reading req_to_token in place) -> o_proj (+all-reduce under TP) ->
+RMSNorm -> gate_up linear -> SiLU*mul -> down linear (+all-reduce).  Embedding lookup, lm_head and sampling are outside
+the hot path and are NOT in the step; this is stated in the JSON (`config.excluded`).
+
+Default workload (N=1) = BASELINE.json configs[1]: Llama-3.1-8B FP8 block-128 W8A8 decode, batch 64 x 4096 ctx,
+page_size 1, shuffled page table, 32 layers each with its own KV pool (34 GB) and weights (7 GB), random init.
+N>1: tensor parallel over the N ranks (KV heads and column/row-parallel linears sharded, NCCL all-reduce after
+o_proj / down_proj), batch 64*N -> per-GPU attention work fixed ("weak" scaling).
+
+The JSON line carries: value (device-timed, CUDA-graph replay, inputs resident), e2e (the same step through the
+plugin API with host buffers: pinned H2D of the step's inputs + D2H of the result inside the timed region),
+roofline (decode-attention kernel, CUDA events, algorithmic bytes / measured HBM peak), cpu_baseline (the
+reference's own CPU kernels, oracle/_ref, or the plain-C port, on a bounded sample), clocks, gpu_launches.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+# ------------------------------------------------------------------------------------------------
+# workloads
+# ------------------------------------------------------------------------------------------------
+WORKLOADS = {
+    # name: model shape + batch; quant in {"bf16", "fp8", "awq", "int8"}
+    "cfg1": dict(model="Llama-3.2-1B-shaped", layers=16, hidden=2048, hq=32, hkv=8, d=64, inter=8192, quant="bf16",
+                 batch=16, ctx=1024, shared_prefix=0, theta=500000.0),
+    "cfg2": dict(model="Llama-3.1-8B", layers=32, hidden=4096, hq=32, hkv=8, d=128, inter=14336, quant="fp8",
+                 batch=64, ctx=4096, shared_prefix=0, theta=500000.0),
+    "cfg2-int8": dict(model="Llama-3.1-8B", layers=32, hidden=4096, hq=32, hkv=8, d=128, inter=14336, quant="int8",
+                      batch=64, ctx=4096, shared_prefix=0, theta=500000.0),
+    "cfg3": dict(model="Qwen2.5-32B", layers=64, hidden=5120, hq=40, hkv=8, d=128, inter=27648, quant="awq",
+                 batch=128, ctx=4096, shared_prefix=0, theta=1000000.0),
+    "cfg4": dict(model="Llama-3.1-70B", layers=80, hidden=8192, hq=64, hkv=8, d=128, inter=28672, quant="fp8",
+                 batch=256, ctx=8192, shared_prefix=2048, theta=500000.0),
+}
+DEFAULT_WORKLOAD = "cfg2"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--layers", type=int, default=0, help="override the layer count (layer slice); 0 = the model's")
+    ap.add_argument("--batch", type=int, default=0, help="override the per-job batch; 0 = the workload's (x N under TP)")
+    ap.add_argument("--tp", type=int, default=0, help="emulate TP-local shapes on ONE GPU (no collectives); 0 = --gpus")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--kernels", action="store_true", help="also print per-kernel roofline lines to stderr")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampling (B200_PROFILING.md "clocks DURING the timed region")
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm: the decode layer stack on the B200 kernels, through the plugin / op surface
+# ------------------------------------------------------------------------------------------------
+class _Params:
+    pass
+
+
+def _rand_fp8_linear(n, k, dev, gen):
+    """weight [N,K] e4m3 + weight_scale_inv [N/128,K/128] (fp8.py:236-300), random init."""
+    lay = _Params()
+    w = torch.randn(n, k, device=dev, dtype=torch.float32, generator=gen) * 100.0
+    lay.weight = w.clamp_(-448, 448).to(torch.float8_e4m3fn)
+    lay.weight_scale_inv = torch.rand((n + 127) // 128, (k + 127) // 128, device=dev, generator=gen) * 2e-4 + 1e-4
+    return lay
+
+
+def _rand_int8_linear(n, k, dev, gen):
+    """weight stored as the [K,N] column-major view of int8 [N,K]; weight_scale [N,1] (w8a8_int8.py:88-123)."""
+    lay = _Params()
+    w = (torch.randn(n, k, device=dev, generator=gen) * 40).clamp_(-127, 127).round_().to(torch.int8)
+    lay.weight = w.t()
+    lay.weight_scale = torch.rand(n, 1, device=dev, generator=gen) * 4e-4 + 1e-4
+    return lay
+
+
+def _rand_awq_linear(n, k, dev, gen, dtype):
+    """qweight [K,N/8] int32, qzeros [K/128,N/8] int32, scales [K/128,N] half (awq.py:104-184)."""
+    lay = _Params()
+    lay.qweight = torch.randint(0, 2 ** 31 - 1, (k, n // 8), device=dev, dtype=torch.int32, generator=gen)
+    lay.qzeros = torch.randint(0, 2 ** 31 - 1, (k // 128, n // 8), device=dev, dtype=torch.int32, generator=gen)
+    lay.scales = (torch.rand(k // 128, n, device=dev, generator=gen) * 4e-3 + 1e-3).to(dtype)
+    return lay
+
+
+class DecodeStack:
+    """L decoder layers (python/sglang/srt/models/llama.py LlamaDecoderLayer shape) sharded for TP rank `rank`."""
+
+    def __init__(self, wl: dict, layers: int, batch: int, tp: int, rank: int, dev: torch.device, collectives: bool):
+        from iaas_sglang_b200 import compat, linear
+        from iaas_sglang_b200.backend import B200AttnBackend
+
+        self.wl, self.L, self.B, self.tp, self.dev = wl, layers, batch, tp, dev
+        self.collectives = collectives
+        self.dtype = torch.bfloat16
+        hq, hkv, d, hidden, inter = wl["hq"], wl["hkv"], wl["d"], wl["hidden"], wl["inter"]
+        assert hq % tp == 0 and inter % tp == 0 and (hkv % tp == 0 or tp % hkv == 0)
+        self.hq, self.hkv, self.d, self.hidden = hq // tp, max(1, hkv // tp), d, hidden
+        self.inter = inter // tp
+        ctx, shared = wl["ctx"], wl["shared_prefix"]
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(1234 + rank)
+        gen_shared = torch.Generator(device=dev)   # scheduler state is replicated on every TP rank
+        gen_shared.manual_seed(1234)
+
+        # ---- page table: shuffled slots (page_size 1, worst-case scatter); optional RadixAttention shared prefix ----
+        unique = batch * (ctx - shared) + shared
+        self.T = unique
+        perm = torch.randperm(unique, device=dev, generator=gen_shared) + 1  # slot 0 reserved (memory_pool.py:236-239)
+        self.r2t_pool = compat.ReqToTokenPool(batch, ctx, dev)
+        table = self.r2t_pool.req_to_token
+        if shared:
+            table[:, :shared] = perm[:shared].to(torch.int32)[None, :]
+        table[:, shared:] = perm[shared:].view(batch, ctx - shared).to(torch.int32)
+        self.seq_lens_cpu = torch.full((batch,), ctx, dtype=torch.int64)
+        self.kv_pool = compat.MHATokenToKVPool(unique, 1, self.dtype, self.hkv, d, layers, dev)
+        for l in range(layers):
+            self.kv_pool.k_buffer[l].normal_(generator=gen)
+            self.kv_pool.v_buffer[l].normal_(generator=gen)
+
+        runner = compat.ModelRunnerStub(compat.ModelConfigStub(hq, hkv, d, ctx), self.r2t_pool, self.kv_pool, device=dev, tp_size=tp)
+        self.backend = B200AttnBackend(runner)
+        self.attn = [compat.RadixAttention(self.hq, d, d ** -0.5, self.hkv, l) for l in range(layers)]
+
+        # ---- weights ----
+        q = wl["quant"]
+        if q == "fp8":
+            self.method, mk = linear.Fp8BlockLinearMethod(), lambda n, k: _rand_fp8_linear(n, k, dev, gen)
+        elif q == "int8":
+            self.method, mk = linear.W8A8Int8LinearMethod(), lambda n, k: _rand_int8_linear(n, k, dev, gen)
+        elif q == "awq":
+            self.method, mk = linear.AWQLinearMethod(), lambda n, k: _rand_awq_linear(n, k, dev, gen, self.dtype)
+        else:
+            raise SystemExit(f"bench: quant {q} not benchable")
+        self.qkv_dim = (self.hq + 2 * self.hkv) * d
+        self.w_qkv = [mk(self.qkv_dim, hidden) for _ in range(layers)]
+        self.w_o = [mk(hidden, self.hq * d) for _ in range(layers)]
+        self.w_gate_up = [mk(2 * self.inter, hidden) for _ in range(layers)]
+        self.w_down = [mk(hidden, self.inter) for _ in range(layers)]
+        self.norm1 = [torch.ones(hidden, dtype=self.dtype, device=dev) for _ in range(layers)]
+        self.norm2 = [torch.ones(hidden, dtype=self.dtype, device=dev) for _ in range(layers)]
+        self.norm_f = torch.ones(hidden, dtype=self.dtype, device=dev)
+
+        # ---- static step inputs (CUDA-graph buffers, cuda_graph_runner.py:140-187) ----
+        self.hidden_in = torch.zeros(batch, hidden, dtype=self.dtype, device=dev)
+        self.positions = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.seq_lens = torch.ones(batch, dtype=torch.int64, device=dev)
+        self.req_pool_indices = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.out_cache_loc = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.fb = compat.ForwardBatch(compat.ForwardMode.DECODE, batch, req_pool_indices=self.req_pool_indices,
+                                      seq_lens=self.seq_lens, out_cache_loc=self.out_cache_loc, seq_lens_sum=batch * ctx,
+                                      seq_lens_cpu=self.seq_lens_cpu, positions=self.positions,
+                                      req_to_token_pool=self.r2t_pool, token_to_kv_pool=self.kv_pool, attn_backend=self.backend)
+        # host-side (pinned) copies of one step's inputs + the result buffer
+        self.h_hidden = (torch.randn(batch, hidden) * 0.5).to(self.dtype).pin_memory()
+        self.h_positions = torch.full((batch,), ctx - 1, dtype=torch.int64).pin_memory()
+        self.h_seq_lens = self.seq_lens_cpu.clone().pin_memory()
+        self.h_rpi = torch.arange(batch, dtype=torch.int64).pin_memory()
+        self.h_loc = table[:, ctx - 1].to(torch.int64).cpu().pin_memory()
+        self.h_out = torch.empty(batch, hidden, dtype=self.dtype).pin_memory()
+        self.out = None
+        self.graph = None
+
+    # bytes copied per step by upload() / download()
+    def h2d_bytes(self):
+        return sum(t.numel() * t.element_size() for t in (self.h_hidden, self.h_positions, self.h_seq_lens, self.h_rpi, self.h_loc))
+
+    def d2h_bytes(self):
+        return self.h_out.numel() * self.h_out.element_size()
+
+    def upload(self):
+        self.hidden_in.copy_(self.h_hidden, non_blocking=True)
+        self.positions.copy_(self.h_positions, non_blocking=True)
+        self.seq_lens.copy_(self.h_seq_lens, non_blocking=True)
+        self.req_pool_indices.copy_(self.h_rpi, non_blocking=True)
+        self.out_cache_loc.copy_(self.h_loc, non_blocking=True)
+
+    def download(self):
+        self.h_out.copy_(self.out, non_blocking=True)
+
+    def _row_parallel(self, layer, x):
+        from iaas_sglang_b200 import linear
+
+        return linear.row_parallel_forward(self.method, layer, x, None, reduce_results=self.collectives)
+
+    def forward(self) -> torch.Tensor:
+        """One decode step over the static buffers (eager; also the body that gets graph-captured)."""
+        from iaas_sglang_b200 import ops
+
+        fb, d = self.fb, self.d
+        h = self.hidden_in
+        residual = torch.zeros_like(h)
+        for l in range(self.L):
+            x = ops.rmsnorm(h, self.norm1[l], 1e-5, residual=residual)       # residual += h ; x = norm(residual)
+            qkv = self.method.apply(self.w_qkv[l], x)
+            q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
+            ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
+            a = self.attn[l](q, k, v, fb)
+            h = self._row_parallel(self.w_o[l], a)
+            x = ops.rmsnorm(h, self.norm2[l], 1e-5, residual=residual)
+            gu = self.method.apply(self.w_gate_up[l], x)
+            act = ops.silu_and_mul(gu)
+            h = self._row_parallel(self.w_down[l], act)
+        return ops.rmsnorm(h, self.norm_f, 1e-5, residual=residual)
+
+    def capture(self):
+        from iaas_sglang_b200 import compat
+
+        self.backend.init_cuda_graph_state(self.B, self.B)
+        self.backend.init_forward_metadata_capture_cuda_graph(self.B, self.B, self.req_pool_indices, self.seq_lens, None,
+                                                              compat.ForwardMode.DECODE, None)
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self.out = self.forward()     # warm-up on the side stream (sizes workspaces, sets func attributes)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=s):
+            self.out = self.forward()
+        torch.cuda.synchronize()
+
+    def replay(self):
+        from iaas_sglang_b200 import compat
+
+        self.backend.init_forward_metadata_replay_cuda_graph(self.B, self.req_pool_indices, self.seq_lens, self.B * self.wl["ctx"],
+                                                             None, compat.ForwardMode.DECODE, None, seq_lens_cpu=self.seq_lens_cpu)
+        self.graph.replay()
+
+    # ---- algorithmic work ----
+    def attn_bytes_per_layer(self):
+        B, ctx, d = self.B, self.wl["ctx"], self.d
+        return B * ctx * self.hkv * 2 * d * 2 + B * ctx * 4 + B * self.hq * 2 * d * 2 + B * self.hkv * 2 * d * 2 * 2
+
+    def weight_bytes_per_layer(self):
+        n = self.qkv_dim * self.hidden + self.hidden * self.hq * self.d + 2 * self.inter * self.hidden + self.hidden * self.inter
+        return n * (0.5 if self.wl["quant"] == "awq" else 1.0)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU leg: the reference's own CPU kernels (oracle/_ref) or the plain-C port, on a bounded sample
+# ------------------------------------------------------------------------------------------------
+class CpuLayerSample:
+    """ONE decoder layer's hot path (decode_attention_cpu + the four quantised linears) at the workload's full batch
+    and context, on host cores.  tokens/s = batch / (layer time x n_layers): a bounded sample (1 of L layers per
+    step), extrapolated linearly over the identical layers -- stated in `sample`."""
+
+    def __init__(self, wl: dict, batch: int, threads: int):
+        from oracle import ref_ops
+
+        self.wl, self.B = wl, batch
+        self.use_ref = ref_ops.available()
+        self.kind = "reference" if self.use_ref else "port"
+        torch.set_num_threads(threads)
+        self.threads = threads if self.use_ref else min(threads, int(os.environ.get("OMP_NUM_THREADS", threads)))
+        g = torch.Generator().manual_seed(1234)
+        hq, hkv, d, hidden, inter, ctx = wl["hq"], wl["hkv"], wl["d"], wl["hidden"], wl["inter"], wl["ctx"]
+        T = batch * ctx
+        bf = torch.bfloat16
+        # bf16 noise straight from random 16-bit patterns would hold NaNs; draw small-int noise and scale instead
+        self.k_buf = (torch.randint(-64, 64, (T + 1, hkv, d), generator=g, dtype=torch.int8).to(bf)) / 32
+        self.v_buf = (torch.randint(-64, 64, (T + 1, hkv, d), generator=g, dtype=torch.int8).to(bf)) / 32
+        self.r2t = (torch.randperm(T, generator=g) + 1).view(batch, ctx).to(torch.int32)
+        self.seq_lens = torch.full((batch,), ctx, dtype=torch.int64)
+        self.rpi = torch.arange(batch, dtype=torch.int64)
+        self.loc = self.r2t[:, ctx - 1].to(torch.int64)
+        self.logits = torch.zeros(batch, hq, 8, d + 1, dtype=torch.float32)   # intel_amx_backend.py:36-46
+        self.x = (torch.randn(batch, hidden, generator=g) * 0.5).to(bf)
+        self.shapes = [((hq + 2 * hkv) * d, hidden), (hidden, hq * d), (2 * inter, hidden), (hidden, inter)]
+        self.ws = []
+        for n, k in self.shapes:
+            w = torch.randint(-100, 100, (n, k), generator=g, dtype=torch.int8).to(torch.float32).to(torch.float8_e4m3fn)
+            s = torch.rand(n // 128, k // 128, generator=g) * 2e-4 + 1e-4
+            if self.use_ref:   # prepacked once, like the reference's weight loader (convert_weight_packed, is_vnni=True)
+                w = ref_ops.ops().convert_weight_packed(w)
+            self.ws.append((w, s))
+        self.o = torch.zeros(batch, hq, d, dtype=bf)
+        self.quant = wl["quant"]
+
+    def _linear(self, x, i):
+        w, s = self.ws[i]
+        if self.use_ref:
+            from oracle import ref_ops
+            return ref_ops.ops().fp8_scaled_mm_cpu(x, w, s, [128, 128], None, torch.bfloat16, True)
+        from oracle import cpu_oracle as orc
+        return orc.fp8_w8a16_mm(x, w, s, (128, 128), None, torch.bfloat16)
+
+    def layer(self):
+        wl = self.wl
+        hq, hkv, d = wl["hq"], wl["hkv"], wl["d"]
+        qkv = self._linear(self.x, 0)
+        q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
+        q, k, v = q.reshape(-1, hq, d), k.reshape(-1, hkv, d), v.reshape(-1, hkv, d)
+        if self.use_ref:
+            from oracle import ref_ops
+            ref_ops.decode_attention_cpu(q, self.k_buf, self.v_buf, self.o, k, v, self.loc, self.logits, self.r2t, self.rpi,
+                                         self.seq_lens, d ** -0.5, 0.0)
+        else:
+            from oracle import cpu_oracle as orc
+            orc.decode_attention(q, self.k_buf, self.v_buf, self.o, k, v, self.loc, self.logits, self.r2t, self.rpi,
+                                 self.seq_lens, d ** -0.5, 0.0)
+        h = self._linear(self.o.view(-1, hq * d), 1)
+        gu = self._linear(h, 2)
+        dd = gu.shape[-1] // 2
+        act = torch.nn.functional.silu(gu[:, :dd]) * gu[:, dd:]
+        return self._linear(act, 3)
+
+    def describe(self, n_layers):
+        return (f"1 of {n_layers} layers per step at the full batch {self.B} x {self.wl['ctx']} ctx "
+                f"(decode_attention_cpu + 4 fp8 block linears via fp8_scaled_mm_cpu, W8A16 as the reference's CPU path is); "
+                f"tokens/s = batch / (layer time x {n_layers})")
+
+
+def time_cpu_layers(sample: CpuLayerSample, warmup: int, steps: int, n_layers: int, budget_s: float = 1e9):
+    for _ in range(max(1, warmup)):
+        sample.layer()
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        sample.layer()
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = (time.perf_counter() - t0) / done
+    return sample.B / (dt * n_layers), dt * 1e3, done
+
+
+def run_reference_arm(args, wl, n_layers):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    batch = args.batch or wl["batch"] * max(1, args.gpus)
+    if wl["quant"] != "fp8":
+        print(json.dumps({"impl": "reference", "unavailable": f"CPU leg implemented for the fp8 workloads, not {wl['quant']}"}))
+        return
+    sample = CpuLayerSample(wl, batch, cores)
+    val, ms, done = time_cpu_layers(sample, args.warmup, args.steps, n_layers)
+    line = {
+        "impl": "reference", "metric": "decode tok/s", "value": round(val, 3), "unit": "tok/s", "n_gpus": args.gpus,
+        "steps": done, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16 activations, fp8 e4m3 weights (W8A16 on CPU)", "data": "synthetic",
+        "config": workload_config(wl, args, n_layers, batch, 1),
+        "cpu_baseline": {"value": round(val, 3), "unit": "tok/s", "cores": sample.threads, "kind": sample.kind,
+                         "sample": sample.describe(n_layers)},
+        "e2e": {"value": round(val, 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(wl, args, n_layers, batch, tp):
+    return {
+        "workload": f"{wl['model']} {wl['quant']} decode, batch {batch} x {wl['ctx']} ctx, page_size 1 (shuffled page table)"
+                    + (f", shared prefix {wl['shared_prefix']}" if wl["shared_prefix"] else ""),
+        "name": args.workload, "layers": n_layers, "global_batch": batch, "ctx": wl["ctx"], "parallelism": f"tp{tp}",
+        "l2": "inputs larger than L2 (KV >= 0.5 GB and weights >= 60 MB per layer per GPU, each layer its own buffers)",
+        "excluded": "embedding lookup, lm_head, sampling (outside the hot path, SURVEY 8d)",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+# main
+# ------------------------------------------------------------------------------------------------
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                p = json.load(f)
+            return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def main():
+    args = parse_args()
+    wl = WORKLOADS[args.workload]
+    n_layers = args.layers or wl["layers"]
+    if args.impl == "reference":
+        run_reference_arm(args, wl, n_layers)
+        return
+
+    import torch.distributed as dist
+
+    from iaas_sglang_b200 import _lib, tp as tpmod
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != max(1, args.gpus):
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback); use --impl reference for the CPU arm"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        tpmod.init_distributed("nccl", dev)
+    lib = _lib.load()
+    assert lib.b200_sm_arch() == 100, f"sm_{lib.b200_sm_arch()} is not a B200"
+
+    tp = args.tp or world
+    batch = args.batch or wl["batch"] * world
+    stack = DecodeStack(wl, n_layers, batch, tp, rank if world > 1 else 0, dev, collectives=world > 1)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed value: CUDA-graph replay of the whole layer stack, inputs resident in HBM ----
+    stack.upload()
+    n0 = lib.b200_launch_count()
+    stack.capture()
+    launches_per_step = (lib.b200_launch_count() - n0) // 2   # one eager warm-up + one captured pass
+    for _ in range(max(3, args.warmup)):
+        stack.replay()
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        stack.replay()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1) / args.steps
+
+    # ---- end to end: host buffers -> H2D -> step -> D2H, through the plugin surface ----
+    e2e_ms = None
+    if not args.no_e2e:
+        for _ in range(3):
+            stack.upload(); stack.replay(); stack.download()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            stack.upload()
+            stack.replay()
+            stack.download()
+            torch.cuda.current_stream().synchronize()   # the caller needs the result before the next step
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    clk = clocks.stop()
+
+    # ---- roofline of the dominant kernel (paged decode attention), CUDA events on the launching stream ----
+    from iaas_sglang_b200 import compat
+
+    stack.backend.init_forward_metadata(stack.fb)
+    q = torch.randn(batch, stack.hq * stack.d, device=dev, dtype=torch.bfloat16)
+    k = torch.randn(batch, stack.hkv * stack.d, device=dev, dtype=torch.bfloat16)
+    v = torch.randn(batch, stack.hkv * stack.d, device=dev, dtype=torch.bfloat16)
+    for l in range(min(3, n_layers)):
+        stack.attn[l](q, k, v, stack.fb)
+    reps = max(1, 64 // n_layers)
+    barrier()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    for _ in range(reps):
+        for l in range(n_layers):
+            stack.attn[l](q, k, v, stack.fb)
+    a1.record()
+    barrier()
+    attn_ms = a0.elapsed_time(a1) / (reps * n_layers)
+    attn_bytes = stack.attn_bytes_per_layer()
+    peak, peak_src = measured_peaks()
+    achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
+
+    # max over ranks
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms or 0.0, attn_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_max, attn_ms = t.tolist()
+        e2e_ms = e2e_max if e2e_ms is not None else None
+        achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
+
+    if rank == 0:
+        value = batch / (ms * 1e-3)
+        step_bytes = n_layers * (stack.attn_bytes_per_layer() + stack.weight_bytes_per_layer())
+        line = {
+            "metric": "decode tok/s", "value": round(value, 1), "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp8 e4m3 W8A8 GEMMs (fp32 accumulate), bf16 attention (fp32 softmax)"
+            if wl["quant"] == "fp8" else f"{wl['quant']} GEMMs, bf16 attention (fp32 softmax)",
+            "data": "synthetic (random-init weights, randn KV, shuffled page table, seed 1234)",
+            "config": workload_config(wl, args, n_layers, batch, tp),
+            "e2e": None if e2e_ms is None else {
+                "value": round(batch / (e2e_ms * 1e-3), 1), "unit": "tok/s", "ms_per_step": round(e2e_ms, 4),
+                "h2d_bytes_per_step": stack.h2d_bytes(), "d2h_bytes_per_step": stack.d2h_bytes(),
+                "path": "pinned host -> static graph buffers -> CUDA-graph replay of B200AttnBackend/linear methods -> pinned host, sync per step"},
+            "gpu_launches": launches_per_step * args.steps,
+            "launches_per_step": launches_per_step,
+            "clocks": clk,
+            "roofline": {
+                "kernel": "decode_attn_mma_kernel (+ split merge)", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "ms_per_launch": round(attn_ms, 4), "algorithmic_bytes_per_launch": attn_bytes,
+                "frac_of_nominal_8TBs": round(achieved / 8000.0, 4)},
+            "step_roofline": {"algorithmic_bytes_per_step_per_gpu": int(step_bytes), "hbm_time_ms_at_peak": round(step_bytes / peak / 1e6, 4),
+                              "frac": round(step_bytes / peak / 1e6 / ms, 4)},
+        }
+        if not args.no_cpu_baseline and world == 1 and wl["quant"] == "fp8":
+            try:
+                cores = os.cpu_count() or 1
+                sample = CpuLayerSample(wl, batch, cores)
+                val, cms, done = time_cpu_layers(sample, 1, 1000, n_layers, budget_s=12.0)
+                line["cpu_baseline"] = {"value": round(val, 3), "unit": "tok/s", "cores": sample.threads, "kind": sample.kind,
+                                        "sample": sample.describe(n_layers) + f"; {done} timed layer passes, {cms:.1f} ms each"}
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

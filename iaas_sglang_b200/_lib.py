@@ -94,7 +94,8 @@ SIGNATURES = {
                                   c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p]),
     "b200_silu_and_mul": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
-    "b200_rope_neox": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
+    "b200_rope_neox": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float,
+                             c_void_p]),
 }
 
 _lib: Optional[C.CDLL] = None

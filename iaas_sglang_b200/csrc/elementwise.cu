@@ -208,15 +208,15 @@ __global__ void __launch_bounds__(256) silu_mul_kernel(const uint16_t* __restric
 }
 
 template <bool BF16>
-__global__ void rope_neox_kernel(uint16_t* __restrict__ q, uint16_t* __restrict__ k, const int64_t* __restrict__ pos,
-                                 int Hq, int Hkv, int D, float log2_theta) {
+__global__ void rope_neox_kernel(uint16_t* __restrict__ q, int64_t q_sm, uint16_t* __restrict__ k, int64_t k_sm,
+                                 const int64_t* __restrict__ pos, int Hq, int Hkv, int D, float log2_theta) {
   const int m = blockIdx.x;
   const int half = D / 2;
   const float ps = (float)pos[m];
   const int total = (Hq + Hkv) * half;
   for (int e = threadIdx.x; e < total; e += blockDim.x) {
     const int h = e / half, i = e % half;
-    uint16_t* base = h < Hq ? q + ((int64_t)m * Hq + h) * D : k + ((int64_t)m * Hkv + (h - Hq)) * D;
+    uint16_t* base = h < Hq ? q + (int64_t)m * q_sm + h * D : k + (int64_t)m * k_sm + (h - Hq) * D;
     const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
     float sn, cs;
     sincosf(ps * inv_freq, &sn, &cs);
@@ -347,15 +347,15 @@ extern "C" int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int
   return launched("silu_mul_kernel launch");
 }
 
-extern "C" int b200_rope_neox(void* q, void* k, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D,
+extern "C" int b200_rope_neox(void* q, int64_t q_sm, void* k, int64_t k_sm, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D,
                               float theta, void* stream) {
   B200_REQUIRE(q && k && positions && M >= 0 && D % 2 == 0, B200_ERR_ARG, "rope_neox: bad argument");
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, B200_ERR_UNSUPPORTED, "rope_neox: dtype");
   if (M == 0) return B200_OK;
   if (int rc = require_sm100("rope_neox")) return rc;
   if (dtype == B200_BF16)
-    rope_neox_kernel<true><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, (uint16_t*)k, positions, Hq, Hkv, D, log2f(theta));
+    rope_neox_kernel<true><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
   else
-    rope_neox_kernel<false><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, (uint16_t*)k, positions, Hq, Hkv, D, log2f(theta));
+    rope_neox_kernel<false><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
   return launched("rope_neox_kernel launch");
 }

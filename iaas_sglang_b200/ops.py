@@ -435,9 +435,12 @@ def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
 
 
 def rope_neox_(q: torch.Tensor, k: torch.Tensor, positions: torch.Tensor, head_dim: int, theta: float = 10000.0) -> None:
+    """In-place neox rotary embedding (rotary_embedding.py forward_native, is_neox_style) on q [M, Hq*D] / k [M, Hkv*D];
+    q and k may be column slices of a packed qkv tensor (row stride != width)."""
     dev = require_cuda(q, k, positions)
-    assert q.is_contiguous() and k.is_contiguous() and positions.dtype == torch.int64
     M = positions.numel()
+    q2, k2 = q.view(M, -1) if q.is_contiguous() else q, k.view(M, -1) if k.is_contiguous() else k
+    assert q2.dim() == 2 and k2.dim() == 2 and q2.stride(1) == 1 and k2.stride(1) == 1 and positions.dtype == torch.int64
     with torch.cuda.device(dev):
-        check(load().b200_rope_neox(ptr(q), ptr(k), ptr(positions), DTYPE_CODE[q.dtype], M, q.numel() // (M * head_dim),
-                                    k.numel() // (M * head_dim), head_dim, theta, current_stream(dev)))
+        check(load().b200_rope_neox(ptr(q2), q2.stride(0), ptr(k2), k2.stride(0), ptr(positions), DTYPE_CODE[q.dtype], M,
+                                    q2.shape[1] // head_dim, k2.shape[1] // head_dim, head_dim, theta, current_stream(dev)))

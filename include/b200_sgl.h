@@ -217,9 +217,10 @@ int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qweight, const 
 int b200_rmsnorm(const void* x, void* residual, const void* weight, void* out, int dtype, int M, int H, float eps,
                  void* stream);
 int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int d, void* stream);
-/* in-place neox-style rotary embedding on q [M,Hq,D] and k [M,Hkv,D] (contiguous), positions int64 [M] */
-int b200_rope_neox(void* q, void* k, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D, float theta,
-                   void* stream);
+/* in-place neox-style rotary embedding on q [M,Hq,D] and k [M,Hkv,D] (heads contiguous, row strides in
+ * elements: q and k may be column slices of one packed qkv tensor), positions int64 [M] */
+int b200_rope_neox(void* q, int64_t q_stride_m, void* k, int64_t k_stride_m, const int64_t* positions, int dtype, int M,
+                   int Hq, int Hkv, int D, float theta, void* stream);
 
 #ifdef __cplusplus
 }

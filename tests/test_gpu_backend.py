@@ -74,7 +74,7 @@ def test_mla_forward_decode_through_plugin():
     backend.init_forward_metadata(fb)
     layer = compat.RadixAttention(Hq, 576, c.sm_scale, 1, 0, v_head_dim=512)
     o = backend.forward_decode(c.q.cuda(), c.k_new.cuda(), c.v_new.cuda(), layer, fb)
-    ref, kb, _ = c.oracle()
+    ref, kb, _ = c.oracle(round_p=False)  # exact softmax; see TOL_MLA_LITERAL in test_gpu_decode_attention.py
     assert o.shape == (B, Hq * 512)
     assert rel_l2(o.view(B, Hq, 512), ref) < 2e-3
     assert torch.equal(pool.kv_buffer[0][:T].cpu(), kb)

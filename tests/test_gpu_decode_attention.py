@@ -8,6 +8,10 @@ from tests.util import DecodeCase, golden_decode_cases, max_abs, rel_l2, run_cud
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-3
+# MLA only: the reference's CPU kernel rounds every softmax weight to bf16 before P.V (decode.cpp:1157-1159), which
+# puts its OWN output ~2e-3 (relative L2, randn inputs) away from the exact softmax.  The CUDA kernel is held to
+# 2e-3 against the exact form (fp32 weights) and to 2x that against the reference's literally-rounded output.
+TOL_MLA_LITERAL = 4e-3
 
 
 def check(c: DecodeCase, cap=0.0, fused=False, num_splits=0, write_kv=True):
@@ -15,6 +19,10 @@ def check(c: DecodeCase, cap=0.0, fused=False, num_splits=0, write_kv=True):
     out, kb2, vb2 = run_cuda_decode(c, logit_cap=cap, fused=fused, num_splits=num_splits, write_kv=write_kv)
     assert not torch.isnan(out.float()).any()
     err = rel_l2(out, ref)
+    if c.mla:
+        assert err < TOL_MLA_LITERAL, f"rel_l2 vs reference-rounded {err:.3e}"
+        ref, _, _ = c.oracle(logit_cap=cap, write_kv=write_kv, round_p=False)
+        err = rel_l2(out, ref)
     assert err < TOL, f"rel_l2 {err:.3e} maxabs {max_abs(out, ref):.3e}"
     assert torch.equal(kb, kb2) and torch.equal(vb, vb2), "KV pool differs from the oracle's after the append"
     return out
@@ -56,7 +64,7 @@ def test_against_reference_golden_outputs(case):
     split = (c["seq_lens"] + 7) // 8
     full = (c["seq_lens"] + split - 1) // split == 8
     if full.any():
-        assert rel_l2(out.cpu()[full], c["o"][full]) < TOL
+        assert rel_l2(out.cpu()[full], c["o"][full]) < (TOL_MLA_LITERAL if c["mla"] else TOL)
     exp_k = c["k_buf"].clone()
     exp_k[c["loc"]] = c["key"]
     assert torch.equal(kb.cpu(), exp_k)

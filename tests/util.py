@@ -68,13 +68,15 @@ class DecodeCase:
         self.loc = torch.stack([r2t[rpi[b], int(sl[b]) - 1] for b in range(B)]).to(torch.int64)
         self.sm_scale = 1.0 / (D ** 0.5)
 
-    def oracle(self, logit_cap=0.0, write_kv=True, num_kv_splits=8):
+    def oracle(self, logit_cap=0.0, write_kv=True, num_kv_splits=8, round_p=None):
+        """round_p: the reference's MLA path rounds the softmax weights to bf16 before P.V (decode.cpp:1157-1159);
+        None = as the reference does (MLA only), False = keep them in fp32 (the exact softmax)."""
         kb = self.k_buf.clone()
         vb = kb.narrow(2, 0, self.Dv) if self.mla else self.v_buf.clone()
         out = torch.zeros(self.B, self.Hq, self.Dv, dtype=self.dtype)
         orc.decode_attention(self.q, kb, vb, out, self.k_new if write_kv else None, self.v_new if write_kv else None,
                              self.loc, None, self.req_to_token, self.req_pool_indices, self.seq_lens, self.sm_scale,
-                             logit_cap, num_kv_splits=num_kv_splits, is_mla=self.mla)
+                             logit_cap, num_kv_splits=num_kv_splits, is_mla=self.mla if round_p is None else round_p)
         return out, kb, vb
 
     def cuda(self, device="cuda"):

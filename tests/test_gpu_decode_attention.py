@@ -14,7 +14,7 @@ TOL = 2e-3
 TOL_MLA_LITERAL = 4e-3
 
 
-def check(c: DecodeCase, cap=0.0, fused=False, num_splits=0, write_kv=True):
+def check(c: DecodeCase, cap=0.0, fused=False, num_splits=0, write_kv=True, first_slot=0):
     ref, kb, vb = c.oracle(logit_cap=cap, write_kv=write_kv)
     out, kb2, vb2 = run_cuda_decode(c, logit_cap=cap, fused=fused, num_splits=num_splits, write_kv=write_kv)
     assert not torch.isnan(out.float()).any()
@@ -24,7 +24,10 @@ def check(c: DecodeCase, cap=0.0, fused=False, num_splits=0, write_kv=True):
         ref, _, _ = c.oracle(logit_cap=cap, write_kv=write_kv, round_p=False)
         err = rel_l2(out, ref)
     assert err < TOL, f"rel_l2 {err:.3e} maxabs {max_abs(out, ref):.3e}"
-    assert torch.equal(kb, kb2) and torch.equal(vb, vb2), "KV pool differs from the oracle's after the append"
+    # first_slot=1 skips the reserved dummy slot 0 (memory_pool.py:236-239): several padded rows write it at once,
+    # so its content is whichever write lands last -- unspecified in the reference too
+    assert torch.equal(kb[first_slot:], kb2[first_slot:]) and torch.equal(vb[first_slot:], vb2[first_slot:]), \
+        "KV pool differs from the oracle's after the append"
     return out
 
 
@@ -116,7 +119,8 @@ def test_no_kv_write_and_cuda_graph_padding_rows():
     c = DecodeCase(4, 32, 8, 128, 128, [300, 1, 1, 1])
     c.req_pool_indices[1:] = 0
     c.loc[1:] = 0
-    check(c)
+    check(c, first_slot=1)
+    check(c, first_slot=1, fused=True)
 
 
 def test_unique_slot_indexing_is_exact():

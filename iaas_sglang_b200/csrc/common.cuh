@@ -120,6 +120,14 @@ __device__ __forceinline__ void bulk_g2s_hint(void* dst_smem, const void* src_gm
       "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
 }
+// 16-byte cp.async (LDGSTS, L2 only) and its mbarrier completion hook: the barrier's pending count is NOT
+// incremented, the arrive fires once all of this thread's earlier cp.async have landed
+__device__ __forceinline__ void cp_async_16(uint32_t dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
 }

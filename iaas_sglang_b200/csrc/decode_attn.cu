@@ -25,7 +25,11 @@
 namespace b200 {
 
 constexpr int kConsumerWarps = 8;
-constexpr int kAttnThreads = (kConsumerWarps + 1) * 32;
+// UBLKCP takes its addresses from uniform registers, so a warp issues its lanes' bulk copies one after the
+// other (ncu: a single producer warp was the bottleneck, consumers idle on the full barrier 44 % of the
+// samples).  Four producer warps split every tile's rows and prefetch the page-table entries one tile ahead.
+constexpr int kProducerWarps = 4;
+constexpr int kAttnThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kTokPerWarp = 16;
 constexpr float kLog2e = 1.4426950408889634f;
 
@@ -62,6 +66,11 @@ struct AttnCfg {
   static constexpr int TILE_T = WT * kTokPerWarp;
   static constexpr int ROW_BYTES = HPC * D * 2;
   static constexpr int ROW_PITCH = ROW_BYTES + 16;
+  // rows >= 1 KB go through the TMA bulk-copy engine (one UBLKCP per row); shorter rows (few KV heads per
+  // GPU under TP) are limited by the per-copy cost of that engine (measured: 256 B rows -> 47 % of HBM), so
+  // they are staged with 16-byte cp.async (LDGSTS) instead, tracked by the same mbarriers.
+  static constexpr bool BULK = ROW_BYTES >= 1024;
+  static constexpr int FULL_COUNT = BULK ? kProducerWarps : kProducerWarps * 32;
   static constexpr int KV_BYTES = TILE_T * ROW_PITCH;
   static constexpr int STAGE_BYTES = 2 * KV_BYTES;
   static constexpr int STAGES = (D >= 128) ? 3 : 6;
@@ -98,16 +107,17 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], C::FULL_COUNT);
       mbar_init(&empty[s], kConsumerWarps);
     }
     fence_mbar_init();
   }
   __syncthreads();
 
-  if (warp == kConsumerWarps) {
-    // ================================ producer warp ================================
-    if (p.fused_new && split == 0 && qblk == 0) {
+  if (warp >= kConsumerWarps) {
+    // ================================ producer warps ================================
+    const int pw = warp - kConsumerWarps;
+    if (p.fused_new && split == 0 && qblk == 0 && pw == 0) {
       // fused KVCache.set_kv_buffer for this CTA's heads (memory_pool.py:418-456)
       const uint4* ks = reinterpret_cast<const uint4*>(p.k_new + b * p.kn_sb + kvh0 * p.kn_sh);
       const uint4* vs = reinterpret_cast<const uint4*>(p.v_new + b * p.vn_sb + kvh0 * p.vn_sh);
@@ -118,36 +128,78 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
         vd[i] = vs[i];
       }
     }
-    constexpr int R = (C::TILE_T + 31) / 32;
-    for (int it = 0; it < n_tiles; ++it) {
-      const int s = it % C::STAGES;
-      const uint32_t ph = (it / C::STAGES) & 1;
-      int64_t idx[R];
+    constexpr int RW = C::TILE_T / kProducerWarps;  // token rows per producer warp per tile
+    const uint16_t* knew_row = p.k_new + b * p.kn_sb + kvh0 * p.kn_sh;
+    const uint16_t* vnew_row = p.v_new + b * p.vn_sb + kvh0 * p.vn_sh;
+    if constexpr (C::BULK) {
+      constexpr int ITEMS = 2 * RW;  // one K and one V bulk copy per row
+      constexpr int R = (ITEMS + 31) / 32;
+      int64_t idx[R], nxt[R];
+      auto load_idx = [&](int it, int64_t(&dst)[R]) {
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int j = lane + 32 * r;
-        int64_t pos = kv0 + (int64_t)it * C::TILE_T + j;
-        if (pos > kv1 - 1) pos = kv1 - 1;  // tail: duplicate the last valid row (masked by the consumers)
-        idx[r] = (j < C::TILE_T) ? load_index(p.r2t, req * p.r2t_stride + pos, p.idx64) : 0;
-      }
-      mbar_wait(&empty[s], ph ^ 1);
-      if (lane == 0) mbar_arrive_expect_tx(&full[s], 2 * C::TILE_T * C::ROW_BYTES);
-      __syncwarp();
-      uint8_t* kdst = smem + s * C::STAGE_BYTES;
-      uint8_t* vdst = kdst + C::KV_BYTES;
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int j = lane + 32 * r;
-        if (j < C::TILE_T) {
-          const uint16_t* ksrc = p.k_buf + idx[r] * p.kb_st + kvh0 * p.kb_sh;
-          const uint16_t* vsrc = p.v_buf + idx[r] * p.vb_st + kvh0 * p.vb_sh;
-          if (idx[r] == loc_b) {
-            ksrc = p.k_new + b * p.kn_sb + kvh0 * p.kn_sh;
-            vsrc = p.v_new + b * p.vn_sb + kvh0 * p.vn_sh;
-          }
-          bulk_g2s(kdst + j * C::ROW_PITCH, ksrc, C::ROW_BYTES, &full[s]);
-          bulk_g2s(vdst + j * C::ROW_PITCH, vsrc, C::ROW_BYTES, &full[s]);
+        for (int r = 0; r < R; ++r) {
+          const int item = lane + 32 * r;
+          int64_t pos = kv0 + (int64_t)it * C::TILE_T + pw * RW + (item >> 1);
+          if (pos > kv1 - 1) pos = kv1 - 1;  // tail: duplicate the last valid row (masked by the consumers)
+          dst[r] = (item < ITEMS) ? load_index(p.r2t, req * p.r2t_stride + pos, p.idx64) : 0;
         }
+      };
+      if (n_tiles > 0) load_idx(0, idx);
+      for (int it = 0; it < n_tiles; ++it) {
+        const int s = it % C::STAGES;
+        const uint32_t ph = (it / C::STAGES) & 1;
+        if (it + 1 < n_tiles) load_idx(it + 1, nxt);
+        mbar_wait(&empty[s], ph ^ 1);
+        if (lane == 0) mbar_arrive_expect_tx(&full[s], ITEMS * C::ROW_BYTES);
+        __syncwarp();
+        uint8_t* kdst = smem + s * C::STAGE_BYTES;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int item = lane + 32 * r;
+          if (item < ITEMS) {
+            const int row = pw * RW + (item >> 1);
+            const bool is_v = item & 1;
+            const uint16_t* src = is_v ? p.v_buf + idx[r] * p.vb_st + kvh0 * p.vb_sh : p.k_buf + idx[r] * p.kb_st + kvh0 * p.kb_sh;
+            if (idx[r] == loc_b) src = is_v ? vnew_row : knew_row;
+            bulk_g2s(kdst + (is_v ? C::KV_BYTES : 0) + row * C::ROW_PITCH, src, C::ROW_BYTES, &full[s]);
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) idx[r] = nxt[r];
+      }
+    } else {
+      // 16-byte cp.async: CPR lanes per row, 32 / CPR rows per warp instruction
+      constexpr int CPR = C::ROW_BYTES / 16;
+      static_assert(CPR <= 32 && 32 % CPR == 0 && RW <= 32, "short-row producer layout");
+      constexpr int RPI = 32 / CPR;
+      const int sub = lane / CPR, chunk = lane % CPR;
+      auto load_idx = [&](int it) -> int64_t {
+        int64_t pos = kv0 + (int64_t)it * C::TILE_T + pw * RW + lane;
+        if (pos > kv1 - 1) pos = kv1 - 1;
+        return lane < RW ? load_index(p.r2t, req * p.r2t_stride + pos, p.idx64) : 0;
+      };
+      int64_t idx = n_tiles > 0 ? load_idx(0) : 0;
+      for (int it = 0; it < n_tiles; ++it) {
+        const int s = it % C::STAGES;
+        const uint32_t ph = (it / C::STAGES) & 1;
+        int64_t nxt = 0;
+        if (it + 1 < n_tiles) nxt = load_idx(it + 1);
+        mbar_wait(&empty[s], ph ^ 1);
+        const uint32_t kdst = smem_u32(smem + s * C::STAGE_BYTES) + (pw * RW + sub) * C::ROW_PITCH + chunk * 16;
+#pragma unroll
+        for (int r = 0; r < RW; r += RPI) {
+          const int64_t ri = __shfl_sync(0xffffffffu, idx, r + sub);
+          const uint16_t* ks = p.k_buf + ri * p.kb_st + kvh0 * p.kb_sh;
+          const uint16_t* vs = p.v_buf + ri * p.vb_st + kvh0 * p.vb_sh;
+          if (ri == loc_b) {
+            ks = knew_row;
+            vs = vnew_row;
+          }
+          cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 8);
+          cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 8);
+        }
+        cp_async_mbar_arrive_noinc(&full[s]);
+        idx = nxt;
       }
     }
     return;

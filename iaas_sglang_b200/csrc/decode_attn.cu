@@ -45,8 +45,8 @@ struct DecodeKParams {
   uint16_t* v_buf;
   int64_t vb_st, vb_sh;
   uint16_t* out;
-  float* part_o;    // [B, Hq, S, Dv]
-  float* part_lse;  // [B, Hq, S]   (log2 domain)
+  float* part_o;    // generic path: [B, Hq, S, Dv];  tuned path: [grid, 2, HPC*16, Dv]
+  float* part_lse;  // generic path: [B, Hq, S];      tuned path: [grid, 2, HPC*16]   (log2 domain)
   const void* r2t;
   int64_t r2t_stride;
   const int64_t* rpi;
@@ -60,6 +60,10 @@ struct DecodeKParams {
   float sm_scale, logit_cap;
 };
 
+constexpr int kMaxSmem = 232448;  // 227 KB: the sm_100 per-block opt-in limit
+constexpr int kMaxBatchTable = 1024;
+constexpr int kMaxPartials = 256;  // >= launch grid of the tuned kernel (one CTA per SM)
+
 template <int D, int HPC>
 struct AttnCfg {
   static constexpr int WT = kConsumerWarps / HPC;
@@ -72,40 +76,96 @@ struct AttnCfg {
   static constexpr bool BULK = ROW_BYTES >= 1024;
   static constexpr int FULL_COUNT = BULK ? kProducerWarps : kProducerWarps * 32;
   static constexpr int KV_BYTES = TILE_T * ROW_PITCH;
-  static constexpr int STAGE_BYTES = 2 * KV_BYTES;
-  static constexpr int STAGES = (D >= 128) ? 3 : 6;
+  // a finished stage doubles as the scratch for the cross-warp merge at the end of a segment
   static constexpr int SCRATCH_BYTES = kConsumerWarps * 16 * (D + 2) * 4;
+  static constexpr int STAGE_RAW = 2 * KV_BYTES > SCRATCH_BYTES ? 2 * KV_BYTES : SCRATCH_BYTES;
+  static constexpr int STAGE_BYTES = (STAGE_RAW + 127) / 128 * 128;
+  // per-CTA copy of the batch: tiles prefix, seq_len, request row, new-token slot
+  static constexpr int TABLE_BYTES = kMaxBatchTable * 8 + (kMaxBatchTable + 4) * 4 + 2 * kMaxBatchTable * 4;
+  static constexpr int STAGES_FIT = (kMaxSmem - TABLE_BYTES - 256) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
   static constexpr int RING_BYTES = STAGES * STAGE_BYTES;
-  static constexpr int SMEM_BYTES = (RING_BYTES > SCRATCH_BYTES ? RING_BYTES : SCRATCH_BYTES) + 2 * STAGES * 8 + 16;
+  static constexpr int SMEM_BYTES = RING_BYTES + TABLE_BYTES + 2 * STAGES * 8 + 16;
+  static_assert(STAGES >= 2, "ring too small");
 };
 
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory"); }
+
+// Work partition of the tuned kernel (shared with the merge kernel).  A "unit" is one (request b, kv-head
+// group x q-block g) pair and costs tiles(b) = ceil(seq_len[b] / TILE_T) tiles; units are laid out b-major.
+// CTA c of `grid` owns the flattened tile range [c*W/grid, (c+1)*W/grid), W = NG * sum_b tiles(b): every SM
+// streams the same number of KV bytes whatever the length distribution, and there is one pipeline ramp-up per
+// SM per launch instead of one per (request, split) CTA.
+__device__ __forceinline__ int64_t part_start(int64_t c, int64_t W, int64_t grid) { return c * W / grid; }
+__device__ __forceinline__ int64_t part_owner(int64_t t, int64_t W, int64_t grid) { return ((t + 1) * grid - 1) / W; }
+
+struct SegCursor {
+  // walks the (b, g, tile) space from flattened tile t; tables live in shared memory
+  const int32_t* P;
+  int B, NG;
+  int b, g, tile, tiles_b;
+  int64_t t, t_end;
+  __device__ __forceinline__ void init(const int32_t* P_, int B_, int NG_, int64_t t0, int64_t t1) {
+    P = P_; B = B_; NG = NG_; t = t0; t_end = t1;
+    int lo = 0, hi = B - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if ((int64_t)NG * P[mid + 1] > t0) hi = mid; else lo = mid + 1;
+    }
+    b = lo;
+    tiles_b = P[b + 1] - P[b];
+    const int64_t rem = t0 - (int64_t)NG * P[b];
+    g = tiles_b > 0 ? (int)(rem / tiles_b) : 0;
+    tile = tiles_b > 0 ? (int)(rem - (int64_t)g * tiles_b) : 0;
+  }
+  __device__ __forceinline__ bool done() const { return t >= t_end; }
+  // tiles of the current segment
+  __device__ __forceinline__ int seg_len() const {
+    const int64_t left = t_end - t;
+    const int in_unit = tiles_b - tile;
+    return left < in_unit ? (int)left : in_unit;
+  }
+  __device__ __forceinline__ void advance(int n) {
+    t += n;
+    tile += n;
+    if (tile == tiles_b) {
+      tile = 0;
+      if (++g == NG) {
+        g = 0;
+        do { ++b; } while (b < B && P[b + 1] == P[b]);
+        tiles_b = b < B ? P[b + 1] - P[b] : 0;
+      }
+    }
+  }
+};
 
 template <int D, int HPC, bool BF16>
 __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const __grid_constant__ DecodeKParams p) {
   using C = AttnCfg<D, HPC>;
   constexpr int Dv = D;
   extern __shared__ __align__(128) uint8_t smem[];
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (C::RING_BYTES > C::SCRATCH_BYTES ? C::RING_BYTES : C::SCRATCH_BYTES));
+  int64_t* s_loc = reinterpret_cast<int64_t*>(smem + C::RING_BYTES);
+  int32_t* s_P = reinterpret_cast<int32_t*>(s_loc + kMaxBatchTable);  // [B + 1] exclusive prefix of tiles(b)
+  int32_t* s_len = s_P + kMaxBatchTable + 4;
+  int32_t* s_rpi = s_len + kMaxBatchTable;
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_rpi + kMaxBatchTable);
   uint64_t* empty = full + C::STAGES;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int split = blockIdx.x, b = blockIdx.z;
   const int n_qblk = (p.G + 15) >> 4;
-  const int hg = blockIdx.y / n_qblk, qblk = blockIdx.y - hg * n_qblk;
-  const int kvh0 = hg * HPC;
-  const int64_t len = p.seq_lens[b];
-  const int64_t req = p.rpi[b];
-  const int64_t loc_b = p.fused_new ? p.loc[b] : -1;
+  const int NG = (p.Hkv / HPC) * n_qblk;
 
-  // tile-aligned split of [0, len)
-  const int64_t per_raw = (len + p.num_splits - 1) / p.num_splits;
-  const int64_t per = (per_raw + C::TILE_T - 1) / C::TILE_T * C::TILE_T;
-  const int64_t kv0 = (int64_t)split * per;
-  const int64_t kv1 = (kv0 + per < len) ? kv0 + per : len;
-  const int n_tiles = kv1 > kv0 ? (int)((kv1 - kv0 + C::TILE_T - 1) / C::TILE_T) : 0;
-
+  // ---- batch tables + barriers ----
+  for (int b = threadIdx.x; b < p.B; b += kAttnThreads) {
+    int64_t len = p.seq_lens[b];
+    if (len < 0) len = 0;
+    s_len[b] = (int32_t)len;
+    s_rpi[b] = (int32_t)p.rpi[b];
+    s_loc[b] = p.fused_new ? p.loc[b] : -1;
+    s_P[b + 1] = (int32_t)((len + C::TILE_T - 1) / C::TILE_T);
+  }
   if (threadIdx.x == 0) {
+    s_P[0] = 0;
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(&full[s], C::FULL_COUNT);
       mbar_init(&empty[s], kConsumerWarps);
@@ -113,137 +173,161 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
     fence_mbar_init();
   }
   __syncthreads();
+  if (warp == 0) {  // inclusive scan of tiles(b) into s_P[1..B]
+    const int chunk = (p.B + 31) / 32;
+    const int b0 = lane * chunk, b1 = min(p.B, b0 + chunk);
+    int sum = 0;
+    for (int b = b0; b < b1; ++b) sum += s_P[b + 1];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int run = incl - sum;
+    for (int b = b0; b < b1; ++b) {
+      run += s_P[b + 1];
+      s_P[b + 1] = run;
+    }
+  }
+  __syncthreads();
+
+  const int64_t W = (int64_t)NG * s_P[p.B];
+  const int64_t t_begin = part_start(blockIdx.x, W, gridDim.x), t_end = part_start(blockIdx.x + 1, W, gridDim.x);
+  if (t_begin >= t_end) return;
+  SegCursor cur;
+  cur.init(s_P, p.B, NG, t_begin, t_end);
 
   if (warp >= kConsumerWarps) {
     // ================================ producer warps ================================
     const int pw = warp - kConsumerWarps;
-    if (p.fused_new && split == 0 && qblk == 0 && pw == 0) {
-      // fused KVCache.set_kv_buffer for this CTA's heads (memory_pool.py:418-456)
-      const uint4* ks = reinterpret_cast<const uint4*>(p.k_new + b * p.kn_sb + kvh0 * p.kn_sh);
-      const uint4* vs = reinterpret_cast<const uint4*>(p.v_new + b * p.vn_sb + kvh0 * p.vn_sh);
-      uint4* kd = reinterpret_cast<uint4*>(p.k_buf + loc_b * p.kb_st + kvh0 * p.kb_sh);
-      uint4* vd = reinterpret_cast<uint4*>(p.v_buf + loc_b * p.vb_st + kvh0 * p.vb_sh);
-      for (int i = lane; i < C::ROW_BYTES / 16; i += 32) {
-        kd[i] = ks[i];
-        vd[i] = vs[i];
-      }
-    }
     constexpr int RW = C::TILE_T / kProducerWarps;  // token rows per producer warp per tile
-    const uint16_t* knew_row = p.k_new + b * p.kn_sb + kvh0 * p.kn_sh;
-    const uint16_t* vnew_row = p.v_new + b * p.vn_sb + kvh0 * p.vn_sh;
-    if constexpr (C::BULK) {
-      constexpr int ITEMS = 2 * RW;  // one K and one V bulk copy per row
-      constexpr int R = (ITEMS + 31) / 32;
-      int64_t idx[R], nxt[R];
-      auto load_idx = [&](int it, int64_t(&dst)[R]) {
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const int item = lane + 32 * r;
-          int64_t pos = kv0 + (int64_t)it * C::TILE_T + pw * RW + (item >> 1);
-          if (pos > kv1 - 1) pos = kv1 - 1;  // tail: duplicate the last valid row (masked by the consumers)
-          dst[r] = (item < ITEMS) ? load_index(p.r2t, req * p.r2t_stride + pos, p.idx64) : 0;
+    uint32_t gt = 0;                                // tiles issued so far (ring position)
+    for (; !cur.done();) {
+      const int n = cur.seg_len();
+      const int b = cur.b, hg = cur.g / n_qblk, qblk = cur.g - hg * n_qblk;
+      const int kvh0 = hg * HPC;
+      const int64_t len = s_len[b], req = s_rpi[b], loc_b = s_loc[b];
+      const int64_t kv0 = (int64_t)cur.tile * C::TILE_T;
+      const int64_t kv_end = (int64_t)(cur.tile + n) * C::TILE_T;
+      const int64_t kv1 = kv_end < len ? kv_end : len;
+      const uint16_t* knew_row = p.k_new + b * p.kn_sb + kvh0 * p.kn_sh;
+      const uint16_t* vnew_row = p.v_new + b * p.vn_sb + kvh0 * p.vn_sh;
+      if (p.fused_new && pw == 0 && qblk == 0 && cur.tile + n == cur.tiles_b) {
+        // fused KVCache.set_kv_buffer for this unit's heads (memory_pool.py:418-456); the attention itself
+        // reads the new row straight from k_new / v_new (substituted below), so no ordering is needed
+        const uint4* ks = reinterpret_cast<const uint4*>(knew_row);
+        const uint4* vs = reinterpret_cast<const uint4*>(vnew_row);
+        uint4* kd = reinterpret_cast<uint4*>(p.k_buf + loc_b * p.kb_st + kvh0 * p.kb_sh);
+        uint4* vd = reinterpret_cast<uint4*>(p.v_buf + loc_b * p.vb_st + kvh0 * p.vb_sh);
+        for (int i = lane; i < C::ROW_BYTES / 16; i += 32) {
+          kd[i] = ks[i];
+          vd[i] = vs[i];
         }
-      };
-      if (n_tiles > 0) load_idx(0, idx);
-      for (int it = 0; it < n_tiles; ++it) {
-        const int s = it % C::STAGES;
-        const uint32_t ph = (it / C::STAGES) & 1;
-        if (it + 1 < n_tiles) load_idx(it + 1, nxt);
-        mbar_wait(&empty[s], ph ^ 1);
-        if (lane == 0) mbar_arrive_expect_tx(&full[s], ITEMS * C::ROW_BYTES);
-        __syncwarp();
-        uint8_t* kdst = smem + s * C::STAGE_BYTES;
+      }
+      const uint8_t* r2t_row = reinterpret_cast<const uint8_t*>(p.r2t) + (req * p.r2t_stride) * (p.idx64 ? 8 : 4);
+      if constexpr (C::BULK) {
+        constexpr int ITEMS = 2 * RW;  // one K and one V bulk copy per row
+        constexpr int R = (ITEMS + 31) / 32;
+        // raw page-table words are kept as loaded (no arithmetic on them) so that the prefetch of the next
+        // tile's entries does not stall on the load before this tile's copies are issued
+        int32_t lo[R], hi[R], nlo[R], nhi[R];
+        auto load_idx = [&](int it, int32_t(&dlo)[R], int32_t(&dhi)[R]) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const int item = lane + 32 * r;
-          if (item < ITEMS) {
-            const int row = pw * RW + (item >> 1);
-            const bool is_v = item & 1;
-            const uint16_t* src = is_v ? p.v_buf + idx[r] * p.vb_st + kvh0 * p.vb_sh : p.k_buf + idx[r] * p.kb_st + kvh0 * p.kb_sh;
-            if (idx[r] == loc_b) src = is_v ? vnew_row : knew_row;
-            bulk_g2s(kdst + (is_v ? C::KV_BYTES : 0) + row * C::ROW_PITCH, src, C::ROW_BYTES, &full[s]);
+          for (int r = 0; r < R; ++r) {
+            const int item = lane + 32 * r;
+            int64_t pos = kv0 + (int64_t)it * C::TILE_T + pw * RW + (item >> 1);
+            if (pos > kv1 - 1) pos = kv1 - 1;  // tail: duplicate the last valid row (masked by the consumers)
+            dlo[r] = 0; dhi[r] = 0;
+            if (item < ITEMS) {
+              if (p.idx64) {
+                const int2 w = *reinterpret_cast<const int2*>(r2t_row + pos * 8);
+                dlo[r] = w.x; dhi[r] = w.y;
+              } else {
+                dlo[r] = *reinterpret_cast<const int32_t*>(r2t_row + pos * 4);
+              }
+            }
+          }
+        };
+        load_idx(0, lo, hi);
+        for (int it = 0; it < n; ++it, ++gt) {
+          const int s = gt % C::STAGES;
+          const uint32_t ph = (gt / C::STAGES) & 1;
+          if (it + 1 < n) load_idx(it + 1, nlo, nhi);
+          mbar_wait(&empty[s], ph ^ 1);
+          if (lane == 0) mbar_arrive_expect_tx(&full[s], ITEMS * C::ROW_BYTES);
+          __syncwarp();
+          uint8_t* kdst = smem + s * C::STAGE_BYTES;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const int item = lane + 32 * r;
+            if (item < ITEMS) {
+              const int64_t idx = p.idx64 ? (((int64_t)hi[r] << 32) | (uint32_t)lo[r]) : (int64_t)lo[r];
+              const int row = pw * RW + (item >> 1);
+              const bool is_v = item & 1;
+              const uint16_t* src = is_v ? p.v_buf + idx * p.vb_st + kvh0 * p.vb_sh : p.k_buf + idx * p.kb_st + kvh0 * p.kb_sh;
+              if (idx == loc_b) src = is_v ? vnew_row : knew_row;
+              bulk_g2s(kdst + (is_v ? C::KV_BYTES : 0) + row * C::ROW_PITCH, src, C::ROW_BYTES, &full[s]);
+            }
+          }
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            lo[r] = nlo[r];
+            hi[r] = nhi[r];
           }
         }
-#pragma unroll
-        for (int r = 0; r < R; ++r) idx[r] = nxt[r];
-      }
-    } else {
-      // 16-byte cp.async: CPR lanes per row, 32 / CPR rows per warp instruction
-      constexpr int CPR = C::ROW_BYTES / 16;
-      static_assert(CPR <= 32 && 32 % CPR == 0 && RW <= 32, "short-row producer layout");
-      constexpr int RPI = 32 / CPR;
-      const int sub = lane / CPR, chunk = lane % CPR;
-      auto load_idx = [&](int it) -> int64_t {
-        int64_t pos = kv0 + (int64_t)it * C::TILE_T + pw * RW + lane;
-        if (pos > kv1 - 1) pos = kv1 - 1;
-        return lane < RW ? load_index(p.r2t, req * p.r2t_stride + pos, p.idx64) : 0;
-      };
-      int64_t idx = n_tiles > 0 ? load_idx(0) : 0;
-      for (int it = 0; it < n_tiles; ++it) {
-        const int s = it % C::STAGES;
-        const uint32_t ph = (it / C::STAGES) & 1;
-        int64_t nxt = 0;
-        if (it + 1 < n_tiles) nxt = load_idx(it + 1);
-        mbar_wait(&empty[s], ph ^ 1);
-        const uint32_t kdst = smem_u32(smem + s * C::STAGE_BYTES) + (pw * RW + sub) * C::ROW_PITCH + chunk * 16;
-#pragma unroll
-        for (int r = 0; r < RW; r += RPI) {
-          const int64_t ri = __shfl_sync(0xffffffffu, idx, r + sub);
-          const uint16_t* ks = p.k_buf + ri * p.kb_st + kvh0 * p.kb_sh;
-          const uint16_t* vs = p.v_buf + ri * p.vb_st + kvh0 * p.vb_sh;
-          if (ri == loc_b) {
-            ks = knew_row;
-            vs = vnew_row;
+      } else {
+        // 16-byte cp.async: CPR lanes per row, 32 / CPR rows per warp instruction
+        constexpr int CPR = C::ROW_BYTES / 16;
+        static_assert(CPR <= 32 && 32 % CPR == 0 && RW <= 32, "short-row producer layout");
+        constexpr int RPI = 32 / CPR;
+        const int sub = lane / CPR, chunk = lane % CPR;
+        int32_t lo = 0, hi = 0, nlo = 0, nhi = 0;
+        auto load_idx = [&](int it, int32_t& dlo, int32_t& dhi) {
+          int64_t pos = kv0 + (int64_t)it * C::TILE_T + pw * RW + lane;
+          if (pos > kv1 - 1) pos = kv1 - 1;
+          if (lane < RW) {
+            if (p.idx64) {
+              const int2 w = *reinterpret_cast<const int2*>(r2t_row + pos * 8);
+              dlo = w.x; dhi = w.y;
+            } else {
+              dlo = *reinterpret_cast<const int32_t*>(r2t_row + pos * 4);
+            }
           }
-          cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 8);
-          cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 8);
+        };
+        load_idx(0, lo, hi);
+        for (int it = 0; it < n; ++it, ++gt) {
+          const int s = gt % C::STAGES;
+          const uint32_t ph = (gt / C::STAGES) & 1;
+          if (it + 1 < n) load_idx(it + 1, nlo, nhi);
+          mbar_wait(&empty[s], ph ^ 1);
+          const int64_t idx = p.idx64 ? (((int64_t)hi << 32) | (uint32_t)lo) : (int64_t)lo;
+          const uint32_t kdst = smem_u32(smem + s * C::STAGE_BYTES) + (pw * RW + sub) * C::ROW_PITCH + chunk * 16;
+#pragma unroll
+          for (int r = 0; r < RW; r += RPI) {
+            const int64_t ri = __shfl_sync(0xffffffffu, idx, r + sub);
+            const uint16_t* ks = p.k_buf + ri * p.kb_st + kvh0 * p.kb_sh;
+            const uint16_t* vs = p.v_buf + ri * p.vb_st + kvh0 * p.vb_sh;
+            if (ri == loc_b) {
+              ks = knew_row;
+              vs = vnew_row;
+            }
+            cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 8);
+            cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 8);
+          }
+          cp_async_mbar_arrive_noinc(&full[s]);
+          lo = nlo;
+          hi = nhi;
         }
-        cp_async_mbar_arrive_noinc(&full[s]);
-        idx = nxt;
       }
+      cur.advance(n);
     }
     return;
   }
 
   // ================================ consumer warps ================================
   const int wh = warp / C::WT, wt = warp - wh * C::WT;
-  const int kvh = kvh0 + wh;
-  const int row0 = qblk * 16;                         // first row of the GQA group handled here
-  const int rows_valid = min(16, p.G - row0);
-  const int qh0 = kvh * p.G + row0;
   const int g = lane >> 2, t = lane & 3;
-
-  if (n_tiles == 0) {
-    // empty split: lse = -inf so that the merge ignores it (cf. decode.cpp:986 writes nothing)
-    if (wt == 0) {
-      if (p.num_splits > 1) {
-        for (int r = lane; r < rows_valid; r += 32)
-          p.part_lse[((int64_t)b * p.Hq + qh0 + r) * p.num_splits + split] = -INFINITY;
-      } else {  // seq_len == 0: defined output (zeros)
-        for (int e = lane; e < rows_valid * Dv; e += 32) p.out[((int64_t)b * p.Hq + qh0) * Dv + e] = 0;
-      }
-    }
-    return;
-  }
-
-  uint32_t qf[D / 16][4];
-  {
-    const uint16_t* q0 = p.q + b * p.q_sb + (int64_t)(qh0 + g) * p.q_sh + 2 * t;
-    const uint16_t* q1 = q0 + 8 * p.q_sh;
-    const bool v0 = g < rows_valid, v1 = g + 8 < rows_valid;
-#pragma unroll
-    for (int ks = 0; ks < D / 16; ++ks) {
-      qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16) : 0u;
-      qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16) : 0u;
-      qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 8) : 0u;
-      qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 8) : 0u;
-    }
-  }
-  float o[Dv / 8][4];
-#pragma unroll
-  for (int j = 0; j < Dv / 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
-  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
-
   const bool has_cap = p.logit_cap > 0.f;
   const float scale2 = p.sm_scale * kLog2e;
   const int lm = lane >> 3, lr = lane & 7;
@@ -251,144 +335,284 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
   const uint32_t k_lane_off = (uint32_t)(((lm >> 1) * 8 + lr) * C::ROW_PITCH + (lm & 1) * 16);
   const uint32_t v_lane_off = (uint32_t)(((lm & 1) * 8 + lr) * C::ROW_PITCH + (lm >> 1) * 16);
   const uint32_t smem_base = smem_u32(smem);
+  uint32_t gt = 0;
 
-  for (int it = 0; it < n_tiles; ++it) {
-    const int s = it % C::STAGES;
-    const uint32_t ph = (it / C::STAGES) & 1;
-    mbar_wait(&full[s], ph);
-    const uint32_t kbase = smem_base + s * C::STAGE_BYTES + (wt * kTokPerWarp) * C::ROW_PITCH + wh * D * 2;
-    const uint32_t vbase = kbase + C::KV_BYTES;
+  for (; !cur.done();) {
+    const int n = cur.seg_len();
+    const int b = cur.b, hg = cur.g / n_qblk, qblk = cur.g - hg * n_qblk;
+    const int kvh0 = hg * HPC, kvh = kvh0 + wh;
+    const int row0 = qblk * 16;  // first row of the GQA group handled here
+    const int rows_valid = min(16, p.G - row0);
+    const int qh0 = kvh * p.G + row0;
+    const int64_t len = s_len[b];
+    const int64_t kv0 = (int64_t)cur.tile * C::TILE_T;
+    const int64_t kv_end = (int64_t)(cur.tile + n) * C::TILE_T;
+    const int64_t kv1 = kv_end < len ? kv_end : len;
+    const bool whole_unit = (cur.tile == 0 && n == cur.tiles_b);
+    const bool first_seg = (cur.t == t_begin);
 
-    float sc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    uint32_t qf[D / 16][4];
+    {
+      const uint16_t* q0 = p.q + b * p.q_sb + (int64_t)(qh0 + g) * p.q_sh + 2 * t;
+      const uint16_t* q1 = q0 + 8 * p.q_sh;
+      const bool v0 = g < rows_valid, v1 = g + 8 < rows_valid;
 #pragma unroll
-    for (int ks = 0; ks < D / 16; ++ks) {
-      uint32_t r0, r1, r2, r3;
-      ldsm_x4(kbase + k_lane_off + ks * 32, r0, r1, r2, r3);
-      mma_16816<BF16>(sc[0], qf[ks], r0, r1);
-      mma_16816<BF16>(sc[1], qf[ks], r2, r3);
-    }
-    const int64_t tok0 = kv0 + (int64_t)it * C::TILE_T + wt * kTokPerWarp;
-    float mx[2] = {-INFINITY, -INFINITY};
-#pragma unroll
-    for (int nt = 0; nt < 2; ++nt)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        float v = sc[nt][e];
-        if (has_cap) {
-          v *= p.sm_scale;
-          v = p.logit_cap * tanhf(v / p.logit_cap) * kLog2e;
-        } else {
-          v *= scale2;
-        }
-        const int64_t pos = tok0 + nt * 8 + 2 * t + (e & 1);
-        if (pos >= kv1) v = -INFINITY;
-        sc[nt][e] = v;
-        mx[e >> 1] = fmaxf(mx[e >> 1], v);
+      for (int ks = 0; ks < D / 16; ++ks) {
+        qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16) : 0u;
+        qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16) : 0u;
+        qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 8) : 0u;
+        qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 8) : 0u;
       }
-    float alpha[2], m_use[2];
+    }
+    float o[Dv / 8][4];
+#pragma unroll
+    for (int j = 0; j < Dv / 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+    int s_last = 0;
+
+    for (int it = 0; it < n; ++it, ++gt) {
+      const int s = gt % C::STAGES;
+      const uint32_t ph = (gt / C::STAGES) & 1;
+      s_last = s;
+      mbar_wait(&full[s], ph);
+      const uint32_t kbase = smem_base + s * C::STAGE_BYTES + (wt * kTokPerWarp) * C::ROW_PITCH + wh * D * 2;
+      const uint32_t vbase = kbase + C::KV_BYTES;
+
+      float sc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+      for (int ks = 0; ks < D / 16; ++ks) {
+        uint32_t r0, r1, r2, r3;
+        ldsm_x4(kbase + k_lane_off + ks * 32, r0, r1, r2, r3);
+        mma_16816<BF16>(sc[0], qf[ks], r0, r1);
+        mma_16816<BF16>(sc[1], qf[ks], r2, r3);
+      }
+      const int64_t tok0 = kv0 + (int64_t)it * C::TILE_T + wt * kTokPerWarp;
+      float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float v = sc[nt][e];
+          if (has_cap) {
+            v *= p.sm_scale;
+            v = p.logit_cap * tanhf(v / p.logit_cap) * kLog2e;
+          } else {
+            v *= scale2;
+          }
+          const int64_t pos = tok0 + nt * 8 + 2 * t + (e & 1);
+          if (pos >= kv1) v = -INFINITY;
+          sc[nt][e] = v;
+          mx[e >> 1] = fmaxf(mx[e >> 1], v);
+        }
+      float alpha[2], m_use[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+        mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+        const float m_new = fmaxf(m_run[r], mx[r]);
+        m_use[r] = (m_new == -INFINITY) ? 0.f : m_new;
+        alpha[r] = exp2f(m_run[r] - m_use[r]);
+        m_run[r] = m_new;
+      }
+      // P is split into hi + lo half-precision parts (p = hi + lo up to 2^-17) and PV is issued twice,
+      // so the result matches an fp32-P reference (decode.cpp:972-984 keeps P in fp32 for MHA/GQA);
+      // the extra MMAs are free for an HBM-bound kernel.
+      uint32_t pa[4], pb[4];
+      float ps[2] = {0.f, 0.f};
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        const float p0 = exp2f(sc[nt][0] - m_use[0]), p1 = exp2f(sc[nt][1] - m_use[0]);
+        const float p2 = exp2f(sc[nt][2] - m_use[1]), p3 = exp2f(sc[nt][3] - m_use[1]);
+        pa[nt * 2 + 0] = pack_half2<BF16>(p0, p1);
+        pa[nt * 2 + 1] = pack_half2<BF16>(p2, p3);
+        const float2 h01 = unpack_half2<BF16>(pa[nt * 2 + 0]), h23 = unpack_half2<BF16>(pa[nt * 2 + 1]);
+        pb[nt * 2 + 0] = pack_half2<BF16>(p0 - h01.x, p1 - h01.y);
+        pb[nt * 2 + 1] = pack_half2<BF16>(p2 - h23.x, p3 - h23.y);
+        ps[0] += p0 + p1;
+        ps[1] += p2 + p3;
+      }
+      l_run[0] = l_run[0] * alpha[0] + ps[0];
+      l_run[1] = l_run[1] * alpha[1] + ps[1];
+      if (alpha[0] != 1.f || alpha[1] != 1.f) {
+#pragma unroll
+        for (int j = 0; j < Dv / 8; ++j) {
+          o[j][0] *= alpha[0];
+          o[j][1] *= alpha[0];
+          o[j][2] *= alpha[1];
+          o[j][3] *= alpha[1];
+        }
+      }
+#pragma unroll
+      for (int jp = 0; jp < Dv / 16; ++jp) {
+        uint32_t r0, r1, r2, r3;
+        ldsm_x4_t(vbase + v_lane_off + jp * 32, r0, r1, r2, r3);
+        mma_16816<BF16>(o[2 * jp], pa, r0, r1);
+        mma_16816<BF16>(o[2 * jp + 1], pa, r2, r3);
+        mma_16816<BF16>(o[2 * jp], pb, r0, r1);
+        mma_16816<BF16>(o[2 * jp + 1], pb, r2, r3);
+      }
+      if (it + 1 < n) {  // the segment's last stage is released after it has served as merge scratch
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+      }
+    }
+
+    // quad-reduce the row sums
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
-      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
-      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
-      const float m_new = fmaxf(m_run[r], mx[r]);
-      m_use[r] = (m_new == -INFINITY) ? 0.f : m_new;
-      alpha[r] = exp2f(m_run[r] - m_use[r]);
-      m_run[r] = m_new;
+      l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+      l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
     }
-    // P is split into hi + lo half-precision parts (p = hi + lo up to 2^-17) and PV is issued twice,
-    // so the result matches an fp32-P reference (decode.cpp:972-984 keeps P in fp32 for MHA/GQA);
-    // the extra MMAs are free for an HBM-bound kernel.
-    uint32_t pa[4], pb[4];
-    float ps[2] = {0.f, 0.f};
-#pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
-      const float p0 = exp2f(sc[nt][0] - m_use[0]), p1 = exp2f(sc[nt][1] - m_use[0]);
-      const float p2 = exp2f(sc[nt][2] - m_use[1]), p3 = exp2f(sc[nt][3] - m_use[1]);
-      pa[nt * 2 + 0] = pack_half2<BF16>(p0, p1);
-      pa[nt * 2 + 1] = pack_half2<BF16>(p2, p3);
-      const float2 h01 = unpack_half2<BF16>(pa[nt * 2 + 0]), h23 = unpack_half2<BF16>(pa[nt * 2 + 1]);
-      pb[nt * 2 + 0] = pack_half2<BF16>(p0 - h01.x, p1 - h01.y);
-      pb[nt * 2 + 1] = pack_half2<BF16>(p2 - h23.x, p3 - h23.y);
-      ps[0] += p0 + p1;
-      ps[1] += p2 + p3;
-    }
-    l_run[0] = l_run[0] * alpha[0] + ps[0];
-    l_run[1] = l_run[1] * alpha[1] + ps[1];
-    if (alpha[0] != 1.f || alpha[1] != 1.f) {
+
+    // ---- merge the WT token-warps of each head through the stage the consumers still own ----
+    consumer_bar();  // every warp is done reading K/V of the last tile
+    float* scratch = reinterpret_cast<float*>(smem + s_last * C::STAGE_BYTES);  // [warp][16][Dv + 2]
+    {
+      float* my = scratch + (size_t)warp * 16 * (Dv + 2);
 #pragma unroll
       for (int j = 0; j < Dv / 8; ++j) {
-        o[j][0] *= alpha[0];
-        o[j][1] *= alpha[0];
-        o[j][2] *= alpha[1];
-        o[j][3] *= alpha[1];
+        *reinterpret_cast<float2*>(my + g * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
+        *reinterpret_cast<float2*>(my + (g + 8) * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][2], o[j][3]);
+      }
+      if (t == 0) {
+        my[g * (Dv + 2) + Dv] = m_run[0];
+        my[g * (Dv + 2) + Dv + 1] = l_run[0];
+        my[(g + 8) * (Dv + 2) + Dv] = m_run[1];
+        my[(g + 8) * (Dv + 2) + Dv + 1] = l_run[1];
       }
     }
+    consumer_bar();
+    // every consumer thread produces elements of (head h, row r, dv): HPC*rows_valid*Dv elements
+    const int slot_row0 = ((int)blockIdx.x * 2 + (first_seg ? 0 : 1)) * (HPC * 16);
+    const int total = HPC * rows_valid * Dv;
+    for (int e = threadIdx.x; e < total; e += kConsumerWarps * 32) {
+      const int dv = e % Dv;
+      const int r = (e / Dv) % rows_valid;
+      const int h = e / (Dv * rows_valid);
+      const float* base = scratch + (size_t)(h * C::WT) * 16 * (Dv + 2) + r * (Dv + 2);
+      float M = -INFINITY;
 #pragma unroll
-    for (int jp = 0; jp < Dv / 16; ++jp) {
-      uint32_t r0, r1, r2, r3;
-      ldsm_x4_t(vbase + v_lane_off + jp * 32, r0, r1, r2, r3);
-      mma_16816<BF16>(o[2 * jp], pa, r0, r1);
-      mma_16816<BF16>(o[2 * jp + 1], pa, r2, r3);
-      mma_16816<BF16>(o[2 * jp], pb, r0, r1);
-      mma_16816<BF16>(o[2 * jp + 1], pb, r2, r3);
+      for (int w = 0; w < C::WT; ++w) M = fmaxf(M, base[(size_t)w * 16 * (Dv + 2) + Dv]);
+      float L = 0.f, O = 0.f;
+      const float Mu = (M == -INFINITY) ? 0.f : M;
+#pragma unroll
+      for (int w = 0; w < C::WT; ++w) {
+        const float* bw = base + (size_t)w * 16 * (Dv + 2);
+        const float sc_w = exp2f(bw[Dv] - Mu);
+        L += bw[Dv + 1] * sc_w;
+        O += bw[dv] * sc_w;
+      }
+      const float inv = L > 0.f ? 1.f / L : 0.f;
+      if (whole_unit) {
+        const int head = (kvh0 + h) * p.G + row0 + r;
+        p.out[((int64_t)b * p.Hq + head) * Dv + dv] = float_to_half<BF16>(O * inv);
+      } else {
+        const int prow = slot_row0 + h * 16 + r;
+        p.part_o[(int64_t)prow * Dv + dv] = O * inv;
+        if (dv == 0) p.part_lse[prow] = L > 0.f ? M + log2f(L) : -INFINITY;
+      }
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[s]);
+    fence_proxy_async();  // the stage goes back to the async-proxy writers (TMA) after generic writes
+    consumer_bar();
+    if (lane == 0) mbar_arrive(&empty[s_last]);
+    cur.advance(n);
   }
+}
 
-  // quad-reduce the row sums
-#pragma unroll
-  for (int r = 0; r < 2; ++r) {
-    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
-    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+// merge of the units that more than one CTA worked on (decode.cpp:812-860 decode_accumulate_kv_splits;
+// decode_attention.py:492-552 _fwd_kernel_stage2).  grid = B*Hq, block = 128.  Recomputes the partition.
+template <bool BF16>
+__global__ void __launch_bounds__(128) decode_merge_part_kernel(const float* __restrict__ part_o,
+                                                                const float* __restrict__ part_lse,
+                                                                uint16_t* __restrict__ out,
+                                                                const int64_t* __restrict__ seq_lens, int B, int Hq,
+                                                                int Ggrp, int HPC, int tile_t, int NG, int n_qblk,
+                                                                int grid, int Dv) {
+  const int b = blockIdx.x / Hq, h = blockIdx.x - b * Hq;
+  __shared__ int red[2][4];
+  int all = 0, before = 0, mine = 0;
+  for (int i = threadIdx.x; i < B; i += 128) {
+    int64_t len = seq_lens[i];
+    if (len < 0) len = 0;
+    const int tl = (int)((len + tile_t - 1) / tile_t);
+    all += tl;
+    if (i < b) before += tl;
+    if (i == b) mine = tl;
   }
-
-  // ---- merge the WT token-warps of each head through shared memory (ring is idle now) ----
-  consumer_bar();
-  float* scratch = reinterpret_cast<float*>(smem);  // [warp][16][Dv + 2]
-  {
-    float* my = scratch + (size_t)warp * 16 * (Dv + 2);
 #pragma unroll
-    for (int j = 0; j < Dv / 8; ++j) {
-      *reinterpret_cast<float2*>(my + g * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
-      *reinterpret_cast<float2*>(my + (g + 8) * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][2], o[j][3]);
-    }
-    if (t == 0) {
-      my[g * (Dv + 2) + Dv] = m_run[0];
-      my[g * (Dv + 2) + Dv + 1] = l_run[0];
-      my[(g + 8) * (Dv + 2) + Dv] = m_run[1];
-      my[(g + 8) * (Dv + 2) + Dv + 1] = l_run[1];
-    }
+  for (int o = 16; o > 0; o >>= 1) {
+    all += __shfl_xor_sync(0xffffffffu, all, o);
+    before += __shfl_xor_sync(0xffffffffu, before, o);
+    mine += __shfl_xor_sync(0xffffffffu, mine, o);
   }
-  consumer_bar();
-  // every consumer thread produces elements of (head wh', row r, dv): HPC*rows_valid*Dv elements
-  const int tid = threadIdx.x;  // < 256
-  const int total = HPC * rows_valid * Dv;
-  for (int e = tid; e < total; e += kConsumerWarps * 32) {
-    const int dv = e % Dv;
-    const int r = (e / Dv) % rows_valid;
-    const int h = e / (Dv * rows_valid);
-    const float* base = scratch + (size_t)(h * C::WT) * 16 * (Dv + 2) + r * (Dv + 2);
-    float M = -INFINITY;
-#pragma unroll
-    for (int w = 0; w < C::WT; ++w) M = fmaxf(M, base[(size_t)w * 16 * (Dv + 2) + Dv]);
-    float L = 0.f, O = 0.f;
-    const float Mu = (M == -INFINITY) ? 0.f : M;
-#pragma unroll
-    for (int w = 0; w < C::WT; ++w) {
-      const float* bw = base + (size_t)w * 16 * (Dv + 2);
-      const float sc_w = exp2f(bw[Dv] - Mu);
-      L += bw[Dv + 1] * sc_w;
-      O += bw[dv] * sc_w;
+  __shared__ int red_mine[4];
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = all;
+    red[1][threadIdx.x >> 5] = before;
+    red_mine[threadIdx.x >> 5] = mine;
+  }
+  __syncthreads();
+  all = red[0][0] + red[0][1] + red[0][2] + red[0][3];
+  before = red[1][0] + red[1][1] + red[1][2] + red[1][3];
+  const int tiles_b = red_mine[0] + red_mine[1] + red_mine[2] + red_mine[3];
+  uint16_t* orow = out + ((int64_t)b * Hq + h) * Dv;
+  if (tiles_b == 0) {  // seq_len == 0: defined output (zeros)
+    for (int d = threadIdx.x; d < Dv; d += 128) orow[d] = 0;
+    return;
+  }
+  const int kvh = h / Ggrp, within = h - kvh * Ggrp;
+  const int hg = kvh / HPC, hl = kvh - hg * HPC, qblk = within >> 4, r = within & 15;
+  const int g = hg * n_qblk + qblk;
+  const int64_t W = (int64_t)NG * all;
+  const int64_t t0 = (int64_t)NG * before + (int64_t)g * tiles_b, t1 = t0 + tiles_b;
+  const int c0 = (int)part_owner(t0, W, grid), c1 = (int)part_owner(t1 - 1, W, grid);
+  if (c0 == c1) return;  // one CTA saw the whole unit and wrote the output itself
+  // partial (o, lse) pairs of the CTAs c0..c1 (CTAs whose range is empty wrote nothing): weights in parallel
+  const int rows = HPC * 16;
+  __shared__ float s_w[kMaxPartials];
+  __shared__ int s_row[kMaxPartials];
+  __shared__ float s_red[4];
+  const int n = c1 - c0 + 1;  // <= grid <= kMaxPartials
+  for (int i = threadIdx.x; i < n; i += 128) {
+    float lse = -INFINITY;
+    int prow = -1;
+    const int c = c0 + i;
+    const int64_t cs = part_start(c, W, grid);
+    if (cs < part_start(c + 1, W, grid)) {
+      prow = (c * 2 + (t0 <= cs ? 0 : 1)) * rows + hl * 16 + r;
+      lse = part_lse[prow];
     }
-    const int head = (kvh0 + h) * p.G + row0 + r;
-    const float inv = L > 0.f ? 1.f / L : 0.f;
-    if (p.num_splits == 1) {
-      p.out[((int64_t)b * p.Hq + head) * Dv + dv] = float_to_half<BF16>(O * inv);
-    } else {
-      p.part_o[(((int64_t)b * p.Hq + head) * p.num_splits + split) * Dv + dv] = O * inv;
-      if (dv == 0) p.part_lse[((int64_t)b * p.Hq + head) * p.num_splits + split] = L > 0.f ? M + log2f(L) : -INFINITY;
+    s_row[i] = prow;
+    s_w[i] = lse;
+  }
+  __syncthreads();
+  float M = -INFINITY;
+  for (int i = threadIdx.x; i < n; i += 128) M = fmaxf(M, s_w[i]);
+  M = warp_max(M);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = M;
+  __syncthreads();
+  M = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
+  const float Mu = (M == -INFINITY) ? 0.f : M;
+  __syncthreads();
+  float L = 0.f;
+  for (int i = threadIdx.x; i < n; i += 128) {
+    const float w = s_row[i] >= 0 ? exp2f(s_w[i] - Mu) : 0.f;
+    s_w[i] = w;
+    L += w;
+  }
+  L = warp_sum(L);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = L;
+  __syncthreads();
+  L = s_red[0] + s_red[1] + s_red[2] + s_red[3];
+  const float inv = L > 0.f ? 1.f / L : 0.f;
+  for (int d = threadIdx.x; d < Dv; d += 128) {
+    float acc = 0.f;
+#pragma unroll 4
+    for (int i = 0; i < n; ++i) {
+      const float w = s_w[i];
+      if (w > 0.f) acc += w * part_o[(int64_t)s_row[i] * Dv + d];
     }
+    orow[d] = float_to_half<BF16>(acc * inv);
   }
 }
 
@@ -543,26 +767,10 @@ static int pick_hpc(int Hkv) {
 
 static bool mma_path_ok(int Hq, int Hkv, int D, int Dv) { return D == Dv && (D == 64 || D == 128) && Hq % Hkv == 0; }
 
-static int choose_splits(int B, int ctas_per_req, int max_seq_len, int tile_t, int hint) {
-  if (hint > 0) return hint > 64 ? 64 : hint;
-  if (max_seq_len <= 0) max_seq_len = 4096;
-  const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
-  int min_tok = 2 * tile_t > 256 ? 2 * tile_t : 256;
-  int max_s = max_seq_len / min_tok;
-  if (max_s < 1) max_s = 1;
-  if (max_s > 32) max_s = 32;
-  double best = -1.0;
-  int best_s = 1;
-  for (int s = 1; s <= max_s; ++s) {
-    const double ctas = (double)B * ctas_per_req * s;
-    const double waves = ceil(ctas / sms);
-    const double util = ctas / (waves * sms) - 0.004 * s;  // mild bias towards fewer splits
-    if (util > best + 1e-9) {
-      best = util;
-      best_s = s;
-    }
-  }
-  return best_s;
+static int attn_grid() {
+  const int sms = device_sm_count();
+  const int g = sms > 0 ? sms : 148;
+  return g > kMaxPartials ? kMaxPartials : g;
 }
 
 template <int D, int HPC, bool BF16>
@@ -574,10 +782,14 @@ static int launch_mma(const DecodeKParams& kp, cudaStream_t st) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     configured = true;
   }
-  const int n_qblk = (kp.G + 15) / 16;
-  dim3 grid(kp.num_splits, (kp.Hkv / HPC) * n_qblk, kp.B);
+  const int grid = attn_grid();
   kern<<<grid, kAttnThreads, C::SMEM_BYTES, st>>>(kp);
-  return launched("decode_attn_mma_kernel launch");
+  if (int rc = launched("decode_attn_mma_kernel launch")) return rc;
+  const int n_qblk = (kp.G + 15) / 16;
+  decode_merge_part_kernel<BF16><<<kp.B * kp.Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq,
+                                                               kp.G, HPC, C::TILE_T, (kp.Hkv / HPC) * n_qblk, n_qblk, grid,
+                                                               kp.Dv);
+  return launched("decode_merge_part_kernel launch");
 }
 
 template <bool BF16>
@@ -590,6 +802,9 @@ static int dispatch_mma(const DecodeKParams& kp, int hpc, cudaStream_t st) {
   set_error("decode_attn: no mma instantiation for D=%d hpc=%d", kp.D, hpc);
   return B200_ERR_UNSUPPORTED;
 }
+
+// scratch of the tuned path: two partial slots per CTA, each HPC*16 rows of (Dv + 1) floats
+static size_t mma_workspace_bytes(int Dv) { return (size_t)attn_grid() * 2 * (8 * 16) * (Dv + 1) * sizeof(float) + 256; }
 
 template <bool BF16>
 static int launch_generic(const DecodeKParams& kp, cudaStream_t st) {
@@ -608,12 +823,8 @@ using namespace b200;
 
 extern "C" int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv, int max_seq_len, int num_splits_hint) {
   if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv != 0) return 1;
-  if (mma_path_ok(Hq, Hkv, D, Dv)) {
-    const int hpc = pick_hpc(Hkv);
-    const int G = Hq / Hkv;
-    return choose_splits(B, (Hkv / hpc) * ((G + 15) / 16), max_seq_len, (kConsumerWarps / hpc) * kTokPerWarp,
-                         num_splits_hint);
-  }
+  // tuned path: the KV work is partitioned on the device from the actual seq_lens (no fixed split count)
+  if (mma_path_ok(Hq, Hkv, D, Dv)) return 1;
   // generic path: 128-thread CTAs, many per SM -> aim for >= 8 CTAs per SM
   if (num_splits_hint > 0) return num_splits_hint > 64 ? 64 : num_splits_hint;
   if (max_seq_len <= 0) max_seq_len = 4096;
@@ -628,8 +839,9 @@ extern "C" int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv
 }
 
 extern "C" size_t b200_decode_attn_workspace_size(int B, int Hq, int Dv, int num_splits) {
-  if (num_splits <= 1) return 16;
-  return ((size_t)B * Hq * num_splits * (Dv + 1)) * sizeof(float) + 256;
+  const size_t tuned = (Dv == 64 || Dv == 128) ? mma_workspace_bytes(Dv) : 16;
+  const size_t generic = num_splits <= 1 ? 16 : ((size_t)B * Hq * num_splits * (Dv + 1)) * sizeof(float) + 256;
+  return tuned > generic ? tuned : generic;
 }
 
 extern "C" int b200_set_kv_buffer(void* k_buf, int64_t kb_st, int64_t kb_sh, void* v_buf, int64_t vb_st, int64_t vb_sh,
@@ -705,25 +917,40 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
   }
   kp.fused_new = fused ? 1 : 0;
 
-  int S;
   if (mma) {
-    S = choose_splits(a->B, (a->Hkv / hpc) * ((kp.G + 15) / 16), a->max_seq_len, (kConsumerWarps / hpc) * kTokPerWarp,
-                      a->num_splits);
-  } else {
-    S = b200_decode_attn_num_splits(a->B, a->Hq, a->Hkv, a->D, a->Dv, a->max_seq_len, a->num_splits);
+    const size_t need = mma_workspace_bytes(a->Dv);
+    B200_REQUIRE(a->workspace && a->workspace_bytes >= need && ((uintptr_t)a->workspace & 15) == 0, B200_ERR_ARG,
+                 "decode_attn: workspace too small or misaligned (need %zu bytes, have %zu)", need, a->workspace_bytes);
+    kp.num_splits = 1;
+    kp.part_o = (float*)a->workspace;
+    kp.part_lse = kp.part_o + (size_t)attn_grid() * 2 * (8 * 16) * a->Dv;
+    // the kernel keeps a per-CTA copy of the batch in shared memory: larger batches go in chunks
+    for (int b0 = 0; b0 < a->B; b0 += kMaxBatchTable) {
+      DecodeKParams c = kp;
+      c.B = a->B - b0 < kMaxBatchTable ? a->B - b0 : kMaxBatchTable;
+      c.q = kp.q + (int64_t)b0 * kp.q_sb;
+      if (kp.k_new) c.k_new = kp.k_new + (int64_t)b0 * kp.kn_sb;
+      if (kp.v_new) c.v_new = kp.v_new + (int64_t)b0 * kp.vn_sb;
+      c.out = kp.out + (int64_t)b0 * kp.Hq * kp.Dv;
+      c.rpi = kp.rpi + b0;
+      c.seq_lens = kp.seq_lens + b0;
+      if (kp.loc) c.loc = kp.loc + b0;
+      const int rc = a->dtype == B200_BF16 ? dispatch_mma<true>(c, hpc, st) : dispatch_mma<false>(c, hpc, st);
+      if (rc != 0) return rc;
+    }
+    return B200_OK;
   }
+  const int S = b200_decode_attn_num_splits(a->B, a->Hq, a->Hkv, a->D, a->Dv, a->max_seq_len, a->num_splits);
   kp.num_splits = S;
   kp.part_o = nullptr; kp.part_lse = nullptr;
   if (S > 1) {
-    const size_t need = b200_decode_attn_workspace_size(a->B, a->Hq, a->Dv, S);
+    const size_t need = ((size_t)a->B * a->Hq * S * (a->Dv + 1)) * sizeof(float) + 256;
     B200_REQUIRE(a->workspace && a->workspace_bytes >= need && ((uintptr_t)a->workspace & 15) == 0, B200_ERR_ARG,
                  "decode_attn: workspace too small or misaligned (need %zu bytes, have %zu)", need, a->workspace_bytes);
     kp.part_o = (float*)a->workspace;
     kp.part_lse = kp.part_o + (size_t)a->B * a->Hq * S * a->Dv;
   }
-  int rc;
-  if (mma) rc = a->dtype == B200_BF16 ? dispatch_mma<true>(kp, hpc, st) : dispatch_mma<false>(kp, hpc, st);
-  else rc = a->dtype == B200_BF16 ? launch_generic<true>(kp, st) : launch_generic<false>(kp, st);
+  int rc = a->dtype == B200_BF16 ? launch_generic<true>(kp, st) : launch_generic<false>(kp, st);
   if (rc != 0) return rc;
   if (S > 1) {
     if (a->dtype == B200_BF16)

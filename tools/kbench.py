@@ -201,6 +201,23 @@ def bench_awq():
         awq_case(128, n, k)
 
 
+def bench_prof():
+    """few plain launches of the two attention shapes for ncu (-k regex:decode_attn_mma)"""
+    global timeit
+
+    def timeit(fn, n_variants, reps=0, warm=3):  # noqa: F811  (no graph, 4 launches)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn(0); fn(1 % n_variants)
+        e0.record()
+        fn(0); fn(1 % n_variants)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 2
+
+    attn_case("cfg2", 64, 32, 8, 128, 4096)
+    attn_case("cfg3tp4", 128, 10, 2, 128, 4096)
+
+
 def main():
     what = sys.argv[1:] or ["attn", "gemm", "gemm_big", "int8", "awq"]
     print(f"# peaks: HBM {HBM} GB/s, bf16 {BF16_TF} TFLOP/s (MEASURED_PEAKS.json or fallback)")

@@ -20,6 +20,9 @@ int check_cuda(cudaError_t e, const char* what);
 // call right after a <<<>>> launch: counts it (b200_launch_count) and returns the launch status
 int launched(const char* what);
 int device_sm_count();
+// programmatic dependent launch (B200_PDL=0 disables): kernels that support it are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization and order themselves with griddepcontrol.wait
+bool pdl_enabled();
 
 #define B200_REQUIRE(cond, code, ...)  \
   do {                                 \
@@ -58,6 +61,12 @@ __device__ __forceinline__ bool elect_one() {
       : "=r"(pred));
   return pred != 0;
 }
+
+// programmatic dependent launch: wait = all prerequisite grids have completed and their writes are visible
+// (no-op when the kernel was not launched as a programmatic dependent); launch_dependents = the next kernel
+// of the stream may start its prologue now
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------
 // mbarrier

@@ -21,6 +21,7 @@
 // so K is split across CTAs (grid.z); partial tiles meet in an fp32 workspace and the last CTA to
 // arrive (atomic ticket) reduces and writes the tile.
 #include "common.cuh"
+#include "gemm_skinny.h"
 
 namespace b200 {
 
@@ -344,6 +345,7 @@ using namespace b200;
 
 extern "C" size_t b200_gemm_workspace_size(int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 16;
+  if (skinny_applicable(M)) return skinny_workspace_bytes(M, N, K);
   const SplitPlan sp = plan_split(M, N, K);
   if (sp.splits <= 1) return 16;
   return kCounterBytes + (size_t)sp.tiles_m * sp.tiles_n * sp.splits * BM * BN * 4;
@@ -364,6 +366,14 @@ extern "C" int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const vo
   const int arch = b200_sm_arch();
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED,
                "fp8_blockwise_scaled_mm: requires an sm_100 device (got sm_%d); no fallback", arch);
+  if (skinny_applicable(M)) {
+    SkinnyParams sp{};
+    sp.sa = sa; sp.sa_sm = sa_sm; sp.sa_sk = sa_sk;
+    sp.sb = sb; sp.sb_sk = sb_sk; sp.sb_sn = sb_sn;
+    sp.bias = nullptr; sp.out = out; sp.ldo = ldo; sp.out_bf16 = out_dtype == B200_BF16;
+    sp.M = M; sp.N = N; sp.K = K;
+    return launch_skinny<0>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
+  }
   GemmParams gp{};
   gp.sa = sa; gp.sa_sm = sa_sm; gp.sa_sk = sa_sk;
   gp.sb = sb; gp.sb_sk = sb_sk; gp.sb_sn = sb_sn;
@@ -382,7 +392,11 @@ int dense_half_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, cons
   gp.M = M; gp.N = N; gp.K = K * 2;
   return launch_gemm<2>(a, lda * 2, w, ldw * 2, gp, workspace, workspace_bytes, st);
 }
-size_t dense_half_gemm_workspace(int M, int N, int K) { return b200_gemm_workspace_size(M, N, K * 2); }
+size_t dense_half_gemm_workspace(int M, int N, int K) {
+  const SplitPlan sp = plan_split(M, N, K * 2);
+  if (sp.splits <= 1) return 16;
+  return kCounterBytes + (size_t)sp.tiles_m * sp.tiles_n * sp.splits * BM * BN * 4;
+}
 }  // namespace b200
 
 extern "C" int b200_int8_scaled_mm(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa, const float* sb,
@@ -398,6 +412,12 @@ extern "C" int b200_int8_scaled_mm(const void* a, int64_t lda, const void* b, in
   if (M == 0) return B200_OK;
   const int arch = b200_sm_arch();
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "int8_scaled_mm: requires an sm_100 device (got sm_%d); no fallback", arch);
+  if (skinny_applicable(M)) {
+    SkinnyParams sp{};
+    sp.sa = sa; sp.sb = sb; sp.bias = bias; sp.out = out; sp.ldo = ldo; sp.out_bf16 = out_dtype == B200_BF16;
+    sp.M = M; sp.N = N; sp.K = K;
+    return launch_skinny<1>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
+  }
   GemmParams gp{};
   gp.sa = sa; gp.sb = sb; gp.bias = bias; gp.out = out; gp.ldo = ldo; gp.out_bf16 = out_dtype == B200_BF16;
   gp.M = M; gp.N = N; gp.K = K;

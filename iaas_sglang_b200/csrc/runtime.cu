@@ -1,6 +1,7 @@
 // C-ABI plumbing: thread-local error string, device queries, TMA descriptor encoding.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -29,6 +30,15 @@ int launched(const char* what) {
   return check_cuda(cudaGetLastError(), what);
 }
 unsigned long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
 
 int device_sm_count() {
   static int cached[64] = {0};

@@ -218,6 +218,24 @@ def bench_prof():
     attn_case("cfg3tp4", 128, 10, 2, 128, 4096)
 
 
+def bench_profgemm():
+    """a few plain launches of decode-shape GEMMs for ncu (-k regex:gemm_skinny)"""
+    global timeit
+
+    def timeit(fn, n_variants, reps=0, warm=3):  # noqa: F811
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn(0); fn(1 % n_variants)
+        e0.record()
+        fn(2 % n_variants); fn(3 % n_variants)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 2
+
+    fp8_case(64, 28672, 4096)
+    int8_case(64, 28672, 4096)
+    fp8_case(64, 6144, 4096)
+
+
 def main():
     what = sys.argv[1:] or ["attn", "gemm", "gemm_big", "int8", "awq"]
     print(f"# peaks: HBM {HBM} GB/s, bf16 {BF16_TF} TFLOP/s (MEASURED_PEAKS.json or fallback)")

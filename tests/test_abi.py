@@ -44,7 +44,9 @@ def test_size_queries_need_no_gpu():
     s = lib.b200_decode_attn_num_splits(64, 32, 8, 128, 128, 4096, 0)
     assert 1 <= s <= 64
     assert lib.b200_decode_attn_workspace_size(64, 32, 128, s) >= 64 * 32 * s * 129 * 4
-    assert lib.b200_decode_attn_num_splits(64, 32, 8, 128, 128, 4096, 5) == 5
+    # the tuned GQA path partitions KV on the device (always 1); the hint applies to the generic path
+    assert lib.b200_decode_attn_num_splits(64, 32, 8, 128, 128, 4096, 5) == 1
+    assert lib.b200_decode_attn_num_splits(64, 32, 8, 96, 96, 4096, 5) == 5
     assert lib.b200_gemm_workspace_size(64, 4096, 4096) > 16
     assert lib.b200_awq_w4a16_workspace_size(16, 1024, 512) >= 1024 * 512 * 2
 

@@ -1,22 +1,28 @@
-// Decode-shape ("skinny", M <= 256) quantised GEMMs for sm_100a: swap-AB tcgen05 + stream-K.
+// Decode-shape ("skinny", M <= 256) quantised GEMMs for sm_100a: swap-AB tcgen05 + cluster split-K.
 //
 //   MODE 0  fp8_blockwise_scaled_mm  (sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:345-423)
 //   MODE 1  int8_scaled_mm           (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747)
 //
 // At decode M (64..256 tokens) these GEMMs stream the weight once and are bound by HBM, not by the tensor
-// core, so the kernel is built like the attention kernel: keep the copy engine saturated on every SM.
-//   * swap-AB: the WEIGHT tile [128 n x 128 k-bytes] is the UMMA "A" operand (M = 128 lanes of TMEM), the
-//     activations [mt_pad x 128] are the "B" operand (UMMA N = M rounded up to 16): no MMA rows are wasted on
-//     padding and the accumulator is only mt_pad columns wide;
-//   * stream-K: the (n-tile, k-block) units are laid out tile-major and CTA c of `grid` (one per SM) owns units
-//     [c*U/grid, (c+1)*U/grid): every SM streams the same number of weight bytes for ANY (N, K); a tile whose
-//     k-blocks are spread over several CTAs meets in an fp32 workspace (two partial slots per CTA) and the last
-//     CTA to arrive (ticket) sums the partials in fixed CTA order (bit-reproducible) and writes the tile;
-//   * warp 0 = TMA producer (weights evict-first), warp 1 = single-thread tcgen05.mma issuer, warp 2 = TMEM
-//     allocator, warps 4.. = epilogue (one TMEM lane = one output column n per thread).
-//   FP8: every 128-deep k-block lands in its own TMEM buffer (double buffered) and is promoted
-//     acc[m] += tmem[m] * (sa[m,kb] * sb[kb,nb]) in fp32 registers (UMMA has no fp32 block scaling);
-//   INT8: int32 accumulation in TMEM over the CTA's k-range of the tile (exact), scales in the epilogue.
+// core, so the kernel is built to keep the copy engine busy on every SM and to keep everything else short:
+//   * swap-AB: the WEIGHT tile [128 n x 128 k-bytes] is the UMMA "A" operand (128 TMEM lanes), the activations
+//     [mt_pad x 128] are the "B" operand (UMMA N = M rounded up to 16): no MMA rows are spent on padding;
+//   * grid = (n-tiles, S): the S CTAs of one n-tile form a thread-block CLUSTER and split K between them; each
+//     streams its K range through a TMA ring, and the partial tiles meet in DISTRIBUTED SHARED MEMORY as a
+//     reduce-scatter (CTA r sums tokens [r*mt/S, (r+1)*mt/S) of all S partials in fixed order, bit-reproducible,
+//     and writes them) -- no global workspace, no tickets, no L2 round trips.  (The first version was a
+//     persistent stream-K kernel whose partial tiles met in an fp32 global workspace: that fix-up alone cost
+//     10-50 us per launch, profiles/r01_gemm_notes.md.)
+//   * up to two CTAs are resident per SM at M <= 64, so 296 CTA slots take whatever (tiles x S) the shape gives;
+//   * warps 0/3 = TMA producers (weights evict-first, prefetched before the programmatic-launch wait), warp 1 =
+//     single-thread tcgen05.mma issuer, warp 2 = TMEM allocator, warps 4.. = epilogue (one TMEM lane = one
+//     output column n per thread).
+//   FP8: every 128-deep k-block lands in its own TMEM buffer (ring of 2-4) and is promoted
+//     acc[m] += tmem[m] * (sa[m,kb] * sb[kb,nb]) in fp32 registers (UMMA has no fp32 block scaling); the scale
+//     products of the CTA's K range are tabulated in shared memory once, so the k-loop has no global loads and
+//     no CTA barriers;
+//   INT8: int32 accumulation in TMEM over the CTA's K range (exact), integer reduce-scatter, scales at the end.
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "gemm_skinny.h"
@@ -26,43 +32,80 @@ namespace b200 {
 constexpr int SK_BN = 128;  // weight rows per tile (UMMA M)
 constexpr int SK_BK = 128;  // K bytes per pipeline stage (one 128-byte swizzle row, one fp8 scale block)
 constexpr int SK_MAX_STAGES = 12;
-constexpr int SK_SMEM_LIMIT = 232448;
+constexpr int SK_MAX_SPLITS = 8;
+constexpr int SK_NONEPI = 4;    // warps 0..3: warp 1 issues the MMAs, warp 2 allocates tensor memory, warps 0 and 3 are TMA producers
+constexpr int SK_NPROD = 2;
+constexpr int SK_FIXED_SMEM = 1024 /*align*/ + 512 /*barriers*/;
 
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+// shared::cta -> shared::cluster bulk copy, completes (complete_tx) on an mbarrier of the destination CTA
+__device__ __forceinline__ void bulk_s2c(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_cluster),
+               "r"(src_cta), "r"(bytes), "r"(bar_cluster)
+               : "memory");
+}
 
-__device__ __forceinline__ long long sk_start(long long c, long long U, long long G) { return c * U / G; }
-__device__ __forceinline__ long long sk_owner(long long u, long long U, long long G) { return ((u + 1) * G - 1) / U; }
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define SK_STAMP(i)                                                                               \
+  do {                                                                                            \
+    if (p.stamps && threadIdx.x == SK_NONEPI * 32) p.stamps[(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (i)] = gtimer(); \
+  } while (0)
 
 template <int GROUPS>
 __device__ __forceinline__ void sk_epi_bar_all() {
   asm volatile("bar.sync 1, %0;" ::"n"(GROUPS * 128) : "memory");
 }
-__device__ __forceinline__ void sk_epi_bar_group(int grp) {
-  asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");
-}
 
 template <int MODE, int COLS, int GROUPS>
-__global__ void __launch_bounds__((4 + 4 * GROUPS) * 32, 1)
+// (M <= 64: small enough in registers and shared memory for two CTAs per SM -- the prologue and write-out of one
+// overlap the streaming of the other, also across consecutive launches)
+__global__ void __launch_bounds__((SK_NONEPI + 4 * GROUPS) * 32, (COLS * GROUPS <= 64) ? 2 : 1)
 gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x,
                    const __grid_constant__ SkinnyParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // (pointer arithmetic, not an integer round trip: the compiler keeps the shared address space and emits LDS/STS)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  constexpr int BUFCOLS = GROUPS * COLS;
+  constexpr int NBUF = MODE == 0 ? (BUFCOLS <= 128 ? 4 : 2) : 1;
+  constexpr uint32_t kTmemCols = NBUF * BUFCOLS < 32 ? 32 : NBUF * BUFCOLS;
+  constexpr int NE = GROUPS * 128;  // epilogue threads
   const int x_bytes = p.mt_pad * SK_BK;
   const int stage_bytes = SK_BN * SK_BK + x_bytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
   uint64_t* empty = full + SK_MAX_STAGES;
   uint64_t* tfull = empty + SK_MAX_STAGES;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  int* flag = reinterpret_cast<int*>(tmem_slot + 1);
-  float* sbuf = reinterpret_cast<float*>(tmem_slot + 4);  // MODE 0: [GROUPS][2][COLS]; MODE 1: sa[256]
-  int* s_off = reinterpret_cast<int*>(sbuf + 512);        // fix-up: partial-slot index of every contributor (<= 256)
+  uint64_t* tempty = tfull + 4;
+  uint64_t* xbar = tempty + 4;  // split-K exchange: incoming partial slices (one phase per pass)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xbar + 1);
+  float* tab = reinterpret_cast<float*>(smem + p.stages * stage_bytes + 512);  // MODE 0: [tab_cap][mt_pad]; MODE 1: sa[256]
+  // after the k-loop the (drained) stage ring is reused: send[P][128] fp32 then recv[S-1][slice][128]
+  float* send = reinterpret_cast<float*>(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  constexpr int BUFCOLS = GROUPS * COLS;
-  constexpr uint32_t kTmemCols = 2 * BUFCOLS;
-  const long long U = p.units, G = gridDim.x;
-  const long long u0 = sk_start(blockIdx.x, U, G), u1 = sk_start(blockIdx.x + 1, U, G);
-  const int n_units = (int)(u1 - u0);
+  const int tile = blockIdx.x;
+  SK_STAMP(0);
+  const int S = p.splits;
+  const int rank = S > 1 ? (int)cluster_ctarank() : 0;
+  const int kb0 = (int)((long long)rank * p.kb_total / S), kb1 = (int)((long long)(rank + 1) * p.kb_total / S);
+  const int nkb = kb1 - kb0;
+  // k-blocks are visited in a per-tile rotated order so that the CTAs do not all pull the same activation lines from L2 at once
+  const int rot = (p.debug & 16) ? (int)((blockIdx.x * 7u) % (unsigned)nkb) : 0;
+#define SK_KB(i) (kb0 + ((i) + rot >= nkb ? (i) + rot - nkb : (i) + rot))
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_w);
@@ -73,10 +116,11 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < NBUF; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], GROUPS * 128);
+      mbar_init(&tempty[a], NE);
     }
+    mbar_init(xbar, 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
@@ -86,334 +130,271 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
   griddep_launch();  // let the next kernel of the stream start its prologue (no-op without PDL)
 
-  if (warp != 1 && warp < 4) {
-    // ================================ TMA producers ================================
-    // One thread sustains only about one tensor-map copy per ~0.5 us (tools/tma_probe.cu: 148 CTAs streaming
-    // 8 KB boxes reach 2.4 TB/s with one issuing warp, 4.3 with two, 5.1 with four), so three warps issue:
-    // unit i belongs to producer i % 3.
-    constexpr int NP = 3;
-    const int pidx = warp == 0 ? 0 : warp - 1;
-    if (lane == 0) {
-      const uint64_t pol_w = make_policy_evict_first();
-      // weights do not depend on the previous kernel: fill the ring with them before waiting for it
-      const int pre = n_units < p.stages ? n_units : p.stages;
-      for (int i = pidx; i < pre; i += NP) {
-        const long long u = u0 + i;
-        const int tile = (int)(u / p.kb_total), kb = (int)(u - (long long)tile * p.kb_total);
-        mbar_arrive_expect_tx(&full[i], stage_bytes);
-        tma_load_2d_hint(smem + i * stage_bytes, &tma_w, kb * SK_BK, tile * SK_BN, &full[i], pol_w);
-      }
-      griddep_wait();
-      for (int i = pidx; i < pre; i += NP) {
-        const int kb = (int)((u0 + i) % p.kb_total);
-        tma_load_2d(smem + i * stage_bytes + SK_BN * SK_BK, &tma_x, kb * SK_BK, 0, &full[i]);
-      }
-      int i = pidx;
-      while (i < pre) i += NP;
-      long long u = u0 + i;
-      int tile = (int)(u / p.kb_total), kb = (int)(u - (long long)tile * p.kb_total);
-      for (; i < n_units; i += NP) {
-        const int s = i % p.stages;
-        const uint32_t ph = (i / p.stages) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        mbar_arrive_expect_tx(&full[s], stage_bytes);
-        uint8_t* st = smem + s * stage_bytes;
-        tma_load_2d_hint(st, &tma_w, kb * SK_BK, tile * SK_BN, &full[s], pol_w);
-        tma_load_2d(st + SK_BN * SK_BK, &tma_x, kb * SK_BK, 0, &full[s]);
-        kb += NP;
-        while (kb >= p.kb_total) {
-          kb -= p.kb_total;
-          ++tile;
-        }
-      }
+  if (warp < SK_NONEPI && warp != 1 && warp != 2 && lane == 0) {
+    // ================================ TMA producers (k-block i belongs to producer i % SK_NPROD) ================================
+    // One thread keeps only a few tensor copies in flight (measured: ~one box per 0.5 us per issuing thread whatever
+    // the box size, tools/tma_probe.cu), so six warps issue.
+    const int pidx = warp == 0 ? 0 : 1;
+    const uint64_t pol_w = make_policy_evict_first();
+    // weights do not depend on the previous kernel: fill the ring with them before waiting for it
+    const int pre = nkb < p.stages ? nkb : p.stages;
+    for (int i = pidx; i < pre; i += SK_NPROD) {
+      mbar_arrive_expect_tx(&full[i], (p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
+      tma_load_2d_hint(smem + i * stage_bytes, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[i], pol_w);
     }
-    __syncwarp();
-  } else if (warp == 1) {
+    griddep_wait();
+    for (int i = pidx; i < pre; i += SK_NPROD)
+      if (!(p.debug & 8)) tma_load_2d(smem + i * stage_bytes + SK_BN * SK_BK, &tma_x, SK_KB(i) * SK_BK, 0, &full[i]);
+    int i = pidx;
+    while (i < pre) i += SK_NPROD;
+    for (; i < nkb; i += SK_NPROD) {
+      const int s = i % p.stages;
+      const uint32_t ph = (i / p.stages) & 1;
+      mbar_wait(&empty[s], ph ^ 1);
+      mbar_arrive_expect_tx(&full[s], (p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
+      uint8_t* st = smem + s * stage_bytes;
+      tma_load_2d_hint(st, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[s], pol_w);
+      if (!(p.debug & 8)) tma_load_2d(st + SK_BN * SK_BK, &tma_x, SK_KB(i) * SK_BK, 0, &full[s]);
+    }
+  } else if (warp == 1 && lane == 0) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
-      const uint32_t idesc = MODE == 0 ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, SK_BN, p.mt_pad)
-                                       : umma_idesc(2 /*s32*/, 1 /*s8*/, 1, SK_BN, p.mt_pad);
-      int seg = -1;
-      int kb = (int)(u0 % p.kb_total) - 1;
-      for (int i = 0; i < n_units; ++i) {
-        const int s = i % p.stages;
-        const uint32_t ph = (i / p.stages) & 1;
-        if (++kb == p.kb_total) kb = 0;
-        const bool seg_first = (i == 0 || kb == 0), seg_last = (i == n_units - 1 || kb == p.kb_total - 1);
-        if (seg_first) ++seg;
-        const int a = MODE == 0 ? (i & 1) : (seg & 1);
-        if (MODE == 0) mbar_wait(&tempty[a], ((i >> 1) & 1) ^ 1);
-        else if (seg_first) mbar_wait(&tempty[a], ((seg >> 1) & 1) ^ 1);
-        mbar_wait(&full[s], ph);
-        tc_fence_after();
-        const uint32_t w_addr = smem_u32(smem + s * stage_bytes);
-        const uint64_t adesc = umma_desc_k_sw128(w_addr);
-        const uint64_t bdesc = umma_desc_k_sw128(w_addr + SK_BN * SK_BK);
-        const uint32_t d = tmem_base + a * BUFCOLS;
+    const uint32_t idesc = MODE == 0 ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, SK_BN, p.mt_pad)
+                                     : umma_idesc(2 /*s32*/, 1 /*s8*/, 1, SK_BN, p.mt_pad);
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % p.stages;
+      const uint32_t ph = (i / p.stages) & 1;
+      const int a = MODE == 0 ? (i % NBUF) : 0;
+      if (MODE == 0) mbar_wait(&tempty[a], ((i / NBUF) & 1) ^ 1);
+      mbar_wait(&full[s], ph);
+      tc_fence_after();
+      const uint32_t w_addr = smem_u32(smem + s * stage_bytes);
+      const uint64_t adesc = umma_desc_k_sw128(w_addr);
+      const uint64_t bdesc = umma_desc_k_sw128(w_addr + SK_BN * SK_BK);
+      const uint32_t d = tmem_base + a * BUFCOLS;
 #pragma unroll
-        for (int k = 0; k < SK_BK / 32; ++k) {
-          const uint32_t accum = MODE == 0 ? (k > 0) : (!seg_first || k > 0);
-          if (MODE == 0) umma_f8f6f4(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
-          else umma_i8(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
-        }
-        tc_commit(&empty[s]);
-        if (MODE == 0 || seg_last) tc_commit(&tfull[a]);
+      for (int k = 0; k < SK_BK / 32; ++k) {
+        const uint32_t accum = MODE == 0 ? (k > 0) : (i > 0 || k > 0);
+        if (MODE == 0) umma_f8f6f4(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+        else umma_i8(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
       }
-    }
-    __syncwarp();
-  } else if (warp >= 4) {
-    // ================================ epilogue warps ================================
-    const int ew = warp - 4, grp = ew >> 2, quad = ew & 3;  // quad == warp % 4: TMEM lanes [32*quad, +32)
-    const int et = (ew & 3) * 32 + lane;                    // thread index inside the group, 0..127
-    const int row = quad * 32 + lane;                       // output column n inside the tile
-    const int col0 = grp * COLS;                            // first token handled by this group
-    int ncols = p.mt_pad - col0;
-    ncols = ncols < 0 ? 0 : (ncols > COLS ? COLS : ncols);
-    const int nchunk = (ncols + 31) / 32;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + col0;
-    float acc[COLS];
-    griddep_wait();  // activation scales, workspace and the output buffer belong to the stream order
-
-    if (MODE == 1) {  // per-token scales once
-      for (int m = threadIdx.x - 128; m < 256; m += GROUPS * 128) sbuf[m] = m < p.M ? __ldg(p.sa + m) : 0.f;
-      sk_epi_bar_all<GROUPS>();
-    }
-
-    // out[m, n] for this thread's column n of tile t from acc[] (MODE 1: int32 bits -> scales, bias)
-    auto write_tile = [&](int t) {
-      const int n = t * SK_BN + row;
-      if (n >= p.N) return;
-      uint16_t* ocol = reinterpret_cast<uint16_t*>(p.out) + n;
-      float sbn = 1.f, bv = 0.f;
-      if (MODE == 1) {
-        sbn = __ldg(p.sb + n);
-        if (p.bias) {
-          const uint16_t bb = __ldg(reinterpret_cast<const uint16_t*>(p.bias) + n);
-          bv = p.out_bf16 ? half_to_float<true>(bb) : half_to_float<false>(bb);
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < COLS; ++j) {
-        const int m = col0 + j;
-        if (j < ncols && m < p.M) {
-          float v = acc[j];
-          if (MODE == 1) {
-            v = __fmul_rn(__fmul_rn((float)__float_as_int(acc[j]), sbuf[m]), sbn);
-            if (p.bias) v = __fadd_rn(v, bv);
-          }
-          ocol[(size_t)m * p.ldo] = p.out_bf16 ? float_to_half<true>(v) : float_to_half<false>(v);
-        }
-      }
-    };
-    int pending[2], n_pending = 0;  // tiles this CTA holds a partial of (head and/or tail of its unit range)
-
-    int seg = -1;
-    long long seg_u0 = u0;
-    int tile = (int)(u0 / p.kb_total), kb = (int)(u0 - (long long)tile * p.kb_total);
-    // fp8: the scale of the NEXT unit is loaded one iteration ahead (two dependent L2 reads otherwise sit on the
-    // critical path of every k-block)
-    auto load_scale = [&](int t_, int kb_) -> float {
-      const int m = col0 + et;
-      if (et >= COLS || m >= p.M) return 0.f;
-      return __ldg(p.sa + (int64_t)m * p.sa_sm + (int64_t)kb_ * p.sa_sk) * __ldg(p.sb + (int64_t)kb_ * p.sb_sk + (int64_t)t_ * p.sb_sn);
-    };
-    float s_cur = 0.f;
-    if (MODE == 0 && n_units > 0) s_cur = load_scale(tile, kb);
-    for (int i = 0; i < n_units; ++i) {
-      const long long u = u0 + i;
-      if (i > 0 && ++kb == p.kb_total) {
-        kb = 0;
-        ++tile;
-      }
-      const bool seg_first = (i == 0 || kb == 0), seg_last = (i == n_units - 1 || kb == p.kb_total - 1);
-      if (seg_first) {
-        ++seg;
-        seg_u0 = u;
-        if (MODE == 0) {
-#pragma unroll
-          for (int j = 0; j < COLS; ++j) acc[j] = 0.f;
-        }
-      }
-      if (MODE == 0) {
-        // scale vector of this k-block for the group's tokens: s[m] = sa[m,kb] * sb[kb,tile]
-        float* sv = sbuf + (grp * 2 + (i & 1)) * COLS;
-        if (et < COLS) sv[et] = s_cur;
-        if (i + 1 < n_units) {
-          const bool wrap = (kb + 1 == p.kb_total);
-          s_cur = load_scale(wrap ? tile + 1 : tile, wrap ? 0 : kb + 1);
-        }
-        sk_epi_bar_group(grp);
-        const int a = i & 1;
-        mbar_wait(&tfull[a], (i >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < COLS / 32; ++c) {
-          if (c < nchunk && !(p.debug & 2)) {
-            uint32_t r[32];
-            tmem_ld_32x32(lane_addr + a * BUFCOLS + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 s4 = *reinterpret_cast<const float4*>(sv + c * 32 + j);
-              acc[c * 32 + j + 0] = fmaf(__uint_as_float(r[j + 0]), s4.x, acc[c * 32 + j + 0]);
-              acc[c * 32 + j + 1] = fmaf(__uint_as_float(r[j + 1]), s4.y, acc[c * 32 + j + 1]);
-              acc[c * 32 + j + 2] = fmaf(__uint_as_float(r[j + 2]), s4.z, acc[c * 32 + j + 2]);
-              acc[c * 32 + j + 3] = fmaf(__uint_as_float(r[j + 3]), s4.w, acc[c * 32 + j + 3]);
-            }
-          }
-        }
-        tc_fence_before();
-        mbar_arrive(&tempty[a]);
-      }
-      if (!seg_last) continue;
-
-      if (MODE == 1) {
-        const int a = seg & 1;
-        mbar_wait(&tfull[a], (seg >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < COLS / 32; ++c) {
-          if (c < nchunk) {
-            uint32_t r[32];
-            tmem_ld_32x32(lane_addr + a * BUFCOLS + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j) acc[c * 32 + j] = __uint_as_float(r[j]);  // raw int32 bits
-          }
-        }
-        tc_fence_before();
-        mbar_arrive(&tempty[a]);
-      }
-
-      // ---- segment done: a whole tile is written now; a partial one goes to this CTA's workspace slot and
-      //      its ticket / reduction is deferred to the end of the CTA's work, so that the (several dependent
-      //      L2 round trips of the) fix-up never stall the k-loop: measured 27-37 us -> see DESIGN.md ----
-      const bool whole = (seg_u0 == (long long)tile * p.kb_total) && (kb == p.kb_total - 1);
-      if (whole) {
-        write_tile(tile);
-      } else if (!(p.debug & 1)) {
-        const int slot = (seg_u0 == u0) ? 0 : 1;
-        float* mine = p.ws_partial + ((size_t)(blockIdx.x * 2 + slot) * p.mt_pad + col0) * SK_BN + row;
-        if (!(p.debug & 8)) {
-#pragma unroll
-          for (int j = 0; j < COLS; ++j)
-            if (j < ncols) mine[(size_t)j * SK_BN] = acc[j];
-        }
-        pending[n_pending++] = tile;
-      }
-    }
-
-    if (n_pending > 0) {
-      if (!(p.debug & 4)) __threadfence();
-      sk_epi_bar_all<GROUPS>();
-      if (threadIdx.x == 128) {
-        int n_reduce = 0;
-        for (int q = 0; q < n_pending; ++q) {
-          const int t = pending[q];
-          const long long uf = (long long)t * p.kb_total;
-          const int contributors = (int)(sk_owner(uf + p.kb_total - 1, U, G) - sk_owner(uf, U, G)) + 1;
-          const int old = atomicAdd(p.ws_counter + t, 1);
-          if (old == contributors - 1) {   // last to arrive: this CTA reduces the tile
-            p.ws_counter[t] = 0;           // self-reset for the next launch
-            flag[1 + n_reduce++] = t;
-          }
-        }
-        flag[0] = n_reduce;
-        if (n_reduce) __threadfence();
-      }
-    } else if (threadIdx.x == 128) {
-      flag[0] = 0;
+      tc_commit(&empty[s]);
+      if (MODE == 0 || i == nkb - 1) tc_commit(&tfull[a]);
     }
   }
 
+  // ================================ epilogue warps: promote / collect the accumulator ================================
+  const int ew = warp - SK_NONEPI, grp = ew >> 2, quad = ew & 3;  // quad == warp % 4: TMEM lanes [32*quad, +32)
+  const int row = quad * 32 + lane;                       // output column n inside the tile
+  const int col0 = grp * COLS;                            // first token handled by this group
+  const int et_all = threadIdx.x - SK_NONEPI * 32;                   // 0 .. NE-1 for the epilogue threads
+  int ncols = p.mt_pad - col0;
+  ncols = ncols < 0 ? 0 : (ncols > COLS ? COLS : ncols);
+  const int nchunk = (ncols + 31) / 32;
+  float acc[COLS];
+
+  if (warp >= SK_NONEPI) {
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + col0;
+    SK_STAMP(1);
+    griddep_wait();  // activation scales and the output buffer belong to the stream order
+#pragma unroll
+    for (int j = 0; j < COLS; ++j) acc[j] = 0.f;
+
+    if (MODE == 0) {
+      for (int c0 = 0; c0 < nkb; c0 += p.tab_cap) {
+        const int cn = nkb - c0 < p.tab_cap ? nkb - c0 : p.tab_cap;
+        if (c0 > 0) sk_epi_bar_all<GROUPS>();  // everyone is done reading the previous chunk of the table
+        // scale products of this chunk: tab[kbl][m] = sa[m, kb] * sb[kb, tile]
+        for (int e = et_all; e < cn * p.mt_pad; e += NE) {
+          const int kbl = e / p.mt_pad, m = e - kbl * p.mt_pad;
+          const int kb = SK_KB(c0 + kbl);
+          float v = 0.f;
+          if (m < p.M)
+            v = __ldg(p.sa + (int64_t)m * p.sa_sm + (int64_t)kb * p.sa_sk) * __ldg(p.sb + (int64_t)kb * p.sb_sk + (int64_t)tile * p.sb_sn);
+          tab[e] = v;
+        }
+        sk_epi_bar_all<GROUPS>();
+        for (int i = c0; i < c0 + cn; ++i) {
+          const int a = i % NBUF;
+          const float* sv = tab + (i - c0) * p.mt_pad + col0;
+          mbar_wait(&tfull[a], (i / NBUF) & 1);
+          tc_fence_after();
+          if constexpr (COLS == 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(lane_addr + a * BUFCOLS, r);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&tempty[a]);  // the values are in registers: the tensor core may refill the buffer
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 s4 = *reinterpret_cast<const float4*>(sv + j);
+              acc[j + 0] = fmaf(__uint_as_float(r[j + 0]), s4.x, acc[j + 0]);
+              acc[j + 1] = fmaf(__uint_as_float(r[j + 1]), s4.y, acc[j + 1]);
+              acc[j + 2] = fmaf(__uint_as_float(r[j + 2]), s4.z, acc[j + 2]);
+              acc[j + 3] = fmaf(__uint_as_float(r[j + 3]), s4.w, acc[j + 3]);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < COLS / 32; ++c) {
+              if (c < nchunk) {
+                uint32_t r[32];
+                tmem_ld_32x32(lane_addr + a * BUFCOLS + c * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                  const float4 s4 = *reinterpret_cast<const float4*>(sv + c * 32 + j);
+                  acc[c * 32 + j + 0] = fmaf(__uint_as_float(r[j + 0]), s4.x, acc[c * 32 + j + 0]);
+                  acc[c * 32 + j + 1] = fmaf(__uint_as_float(r[j + 1]), s4.y, acc[c * 32 + j + 1]);
+                  acc[c * 32 + j + 2] = fmaf(__uint_as_float(r[j + 2]), s4.z, acc[c * 32 + j + 2]);
+                  acc[c * 32 + j + 3] = fmaf(__uint_as_float(r[j + 3]), s4.w, acc[c * 32 + j + 3]);
+                }
+              }
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty[a]);
+          }
+        }
+      }
+    } else {
+      for (int m = et_all; m < 256; m += NE) tab[m] = m < p.M ? __ldg(p.sa + m) : 0.f;  // per-token scales
+      mbar_wait(&tfull[0], 0);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < COLS / 32; ++c) {
+        if (c < nchunk) {
+          uint32_t r[32];
+          tmem_ld_32x32(lane_addr + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[c * 32 + j] = __uint_as_float(r[j]);  // raw int32 bits
+        }
+      }
+      tc_fence_before();
+    }
+    SK_STAMP(2);
+  }
+
+  // ================================ write-out: [split-K exchange through DSMEM,] sum, coalesced store ================================
+  // pass = up to 128 tokens; within a pass CTA r of the cluster owns tokens [r*slice, (r+1)*slice)
+  const int P = p.mt_pad < 128 ? p.mt_pad : 128;
+  const int passes = (p.mt_pad + P - 1) / P;
+  const int slice = (P + S - 1) / S;
+  float* recv = send + P * SK_BN;  // [S-1][slice][128]: slot (src - me - 1) mod S holds the partial of CTA src
+  for (int ps = 0; ps < passes; ++ps) {
+    const int t0 = ps * P;
+    const int pt = p.mt_pad - t0 < P ? p.mt_pad - t0 : P;
+    const int my0 = rank * slice;
+    int mine = pt - my0;
+    mine = mine < 0 ? 0 : (mine > slice ? slice : mine);
+    // 1. this CTA's partial accumulators of the pass -> send[token][n]  (the ring is drained: the epilogue has seen the last MMA)
+    if (warp >= SK_NONEPI && col0 >= t0 && col0 < t0 + pt) {
+#pragma unroll
+      for (int j = 0; j < COLS; ++j)
+        if (j < ncols) send[(col0 - t0 + j) * SK_BN + row] = acc[j];
+      if (S > 1) fence_proxy_async();  // the bulk copies below read these through the async proxy
+    }
+    if (S > 1) {
+      if (threadIdx.x == SK_NONEPI * 32) mbar_arrive_expect_tx(xbar, (uint32_t)((S - 1) * mine * SK_BN * 4));  // armed before anyone can send
+      __syncwarp();
+      cluster_arrive();  // A: every CTA of the cluster has drained its ring and armed its barrier
+      cluster_wait();
+      SK_STAMP(3);
+      if (threadIdx.x == SK_NONEPI * 32 && !(p.debug & 1)) {
+        for (int o = 0; o < S; ++o) {
+          if (o == rank) continue;
+          const int o0 = o * slice;
+          int on = pt - o0;
+          on = on < 0 ? 0 : (on > slice ? slice : on);
+          if (on == 0) continue;
+          const int slot = (rank - o - 1 + S) % S;
+          bulk_s2c(mapa_u32(smem_u32(recv + slot * slice * SK_BN), (uint32_t)o), smem_u32(send + o0 * SK_BN),
+                   (uint32_t)(on * SK_BN * 4), mapa_u32(smem_u32(xbar), (uint32_t)o));
+        }
+      }
+      SK_STAMP(4);
+      if (warp >= SK_NONEPI && !(p.debug & 1)) mbar_wait(xbar, ps & 1);
+      SK_STAMP(5);
+    } else if (warp >= SK_NONEPI) {
+      sk_epi_bar_all<GROUPS>();
+    }
+    // 2. sum the S partials of the owned tokens in CTA order (bit-reproducible), scale (int8), convert, store:
+    //    a thread owns two adjacent output columns, a warp writes whole 128-byte lines
+    if (warp >= SK_NONEPI) {
+      const int pi = et_all & 63, tq = et_all >> 6;
+      const int n_in = 2 * pi, n = tile * SK_BN + n_in;
+      const bool pair_ok = (n + 1 < p.N) && (p.ldo % 2 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 3) == 0);
+      float sb0 = 1.f, sb1 = 1.f, b0 = 0.f, b1 = 0.f;
+      if (MODE == 1) {
+        sb0 = n < p.N ? __ldg(p.sb + n) : 0.f;
+        sb1 = n + 1 < p.N ? __ldg(p.sb + n + 1) : 0.f;
+        if (p.bias) {
+          const uint16_t* bp = reinterpret_cast<const uint16_t*>(p.bias);
+          const uint16_t u0 = n < p.N ? __ldg(bp + n) : (uint16_t)0, u1 = n + 1 < p.N ? __ldg(bp + n + 1) : (uint16_t)0;
+          b0 = p.out_bf16 ? half_to_float<true>(u0) : half_to_float<false>(u0);
+          b1 = p.out_bf16 ? half_to_float<true>(u1) : half_to_float<false>(u1);
+        }
+      }
+#pragma unroll 2
+      for (int tk = tq; tk < mine; tk += NE / 64) {
+        const int m = t0 + my0 + tk;
+        if (m >= p.M || n >= p.N) continue;
+        float2 v[SK_MAX_SPLITS];
+#pragma unroll
+        for (int s2 = 0; s2 < SK_MAX_SPLITS; ++s2) {
+          if (s2 < S) {
+            const float* src = s2 == rank ? send + (my0 + tk) * SK_BN : recv + (((s2 - rank - 1 + S) % S) * slice + tk) * SK_BN;
+            v[s2] = *reinterpret_cast<const float2*>(src + n_in);
+          }
+        }
+        float o0, o1;
+        if (MODE == 0) {
+          o0 = v[0].x;
+          o1 = v[0].y;
+#pragma unroll
+          for (int s2 = 1; s2 < SK_MAX_SPLITS; ++s2)
+            if (s2 < S) {
+              o0 += v[s2].x;
+              o1 += v[s2].y;
+            }
+        } else {
+          int i0 = __float_as_int(v[0].x), i1 = __float_as_int(v[0].y);
+#pragma unroll
+          for (int s2 = 1; s2 < SK_MAX_SPLITS; ++s2)
+            if (s2 < S) {
+              i0 += __float_as_int(v[s2].x);
+              i1 += __float_as_int(v[s2].y);
+            }
+          const float sam = tab[m];
+          o0 = __fmul_rn(__fmul_rn((float)i0, sam), sb0);
+          o1 = __fmul_rn(__fmul_rn((float)i1, sam), sb1);
+          if (p.bias) {
+            o0 = __fadd_rn(o0, b0);
+            o1 = __fadd_rn(o1, b1);
+          }
+        }
+        uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + (size_t)m * p.ldo + n;
+        if (pair_ok) {
+          *reinterpret_cast<uint32_t*>(dst) = p.out_bf16 ? pack_half2<true>(o0, o1) : pack_half2<false>(o0, o1);
+        } else {
+          dst[0] = p.out_bf16 ? float_to_half<true>(o0) : float_to_half<false>(o0);
+          if (n + 1 < p.N) dst[1] = p.out_bf16 ? float_to_half<true>(o1) : float_to_half<false>(o1);
+        }
+      }
+    }
+    if (S > 1) {
+      __syncwarp();
+      cluster_arrive();  // B: my outgoing copies have been consumed, nobody reads my shared memory any more
+      cluster_wait();
+    } else if (ps + 1 < passes && warp >= SK_NONEPI) {
+      sk_epi_bar_all<GROUPS>();
+    }
+  }
+
+  SK_STAMP(6);
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
-  }
-
-  // ---- fix-up of the tiles this CTA arrived last on: ALL threads reduce the tile as a flat [mt_pad][128]
-  //      array, 4 output columns per thread and step, 4 x 4 independent 16-byte loads in flight per thread.
-  //      (Summing into the row-owner registers issued the loads one by one at 255 registers: 28 us.) ----
-  const int n_reduce = flag[0];
-  constexpr int NT = (4 + 4 * GROUPS) * 32;
-  for (int q = 0; q < n_reduce && !(p.debug & 16); ++q) {
-    const int t = flag[1 + q];
-    const long long uf = (long long)t * p.kb_total;
-    const int c_first = (int)sk_owner(uf, U, G), c_last = (int)sk_owner(uf + p.kb_total - 1, U, G);
-    const int nc = c_last - c_first + 1;
-    __syncthreads();  // s_off is reused between tiles
-    for (int i = threadIdx.x; i < nc; i += NT) {
-      const int c = c_first + i;
-      s_off[i] = c * 2 + ((uf <= sk_start(c, U, G)) ? 0 : 1);
-    }
-    __syncthreads();
-    const int nvec = p.mt_pad * (SK_BN / 4);
-    const bool vec_ok = (p.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 7) == 0);
-    for (int vb = threadIdx.x; vb < nvec; vb += 4 * NT) {
-      float4 sum[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) sum[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int i0 = 0; i0 < nc; i0 += 4) {  // contributors in fixed order: the sum is bit-reproducible
-        float4 x[4][4];
-#pragma unroll
-        for (int ii = 0; ii < 4; ++ii) {
-          const size_t base = (size_t)s_off[i0 + ii < nc ? i0 + ii : nc - 1] * p.mt_pad * SK_BN;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int v = vb + k * NT;
-            x[k][ii] = (v < nvec && i0 + ii < nc)
-                           ? __ldcg(reinterpret_cast<const float4*>(p.ws_partial + base + (size_t)(v >> 5) * SK_BN + (v & 31) * 4))
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-        }
-#pragma unroll
-        for (int ii = 0; ii < 4; ++ii)
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (MODE == 0) {
-              sum[k].x += x[k][ii].x; sum[k].y += x[k][ii].y; sum[k].z += x[k][ii].z; sum[k].w += x[k][ii].w;
-            } else {
-              sum[k].x = __int_as_float(__float_as_int(sum[k].x) + __float_as_int(x[k][ii].x));
-              sum[k].y = __int_as_float(__float_as_int(sum[k].y) + __float_as_int(x[k][ii].y));
-              sum[k].z = __int_as_float(__float_as_int(sum[k].z) + __float_as_int(x[k][ii].z));
-              sum[k].w = __int_as_float(__float_as_int(sum[k].w) + __float_as_int(x[k][ii].w));
-            }
-          }
-      }
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int v = vb + k * NT;
-        if (v >= nvec) continue;
-        const int m = v >> 5, n = t * SK_BN + (v & 31) * 4;
-        if (m >= p.M || n >= p.N) continue;
-        float o4[4] = {sum[k].x, sum[k].y, sum[k].z, sum[k].w};
-        if (MODE == 1) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int ne = n + e < p.N ? n + e : p.N - 1;
-            float val = __fmul_rn(__fmul_rn((float)__float_as_int(o4[e]), sbuf[m]), __ldg(p.sb + ne));
-            if (p.bias) {
-              const uint16_t bb = __ldg(reinterpret_cast<const uint16_t*>(p.bias) + ne);
-              val = __fadd_rn(val, p.out_bf16 ? half_to_float<true>(bb) : half_to_float<false>(bb));
-            }
-            o4[e] = val;
-          }
-        }
-        uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + (size_t)m * p.ldo + n;
-        if (vec_ok && n + 4 <= p.N) {
-          uint2 pk;
-          pk.x = p.out_bf16 ? pack_half2<true>(o4[0], o4[1]) : pack_half2<false>(o4[0], o4[1]);
-          pk.y = p.out_bf16 ? pack_half2<true>(o4[2], o4[3]) : pack_half2<false>(o4[2], o4[3]);
-          *reinterpret_cast<uint2*>(dst) = pk;
-        } else {
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (n + e < p.N) dst[e] = p.out_bf16 ? float_to_half<true>(o4[e]) : float_to_half<false>(o4[e]);
-        }
-      }
-    }
   }
 }
 
@@ -421,46 +402,125 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
 
 namespace b200 {
 
-static int skinny_grid(long long units) {
-  int g = device_sm_count() > 0 ? device_sm_count() : 148;
-  // at least ~4 k-blocks per CTA: below that the fix-up traffic outweighs the extra parallelism
-  const long long cap = units / 4 > 0 ? units / 4 : 1;
-  if (g > cap) g = (int)cap;
-  return g;
-}
-
 static int skinny_mt_pad(int M) { return (M + 15) / 16 * 16; }
 
-size_t skinny_workspace_bytes(int M, int N, int K) {
-  const int mt = skinny_mt_pad(M);
-  const int n_tiles = (N + SK_BN - 1) / SK_BN;
-  const long long units = (long long)n_tiles * ((K + SK_BK - 1) / SK_BK);
-  const size_t counters = ((size_t)n_tiles * 4 + 255) & ~(size_t)255;
-  return counters + (size_t)skinny_grid(units) * 2 * mt * SK_BN * 4;
-}
+// the kernel needs no global workspace any more (the K slices meet in distributed shared memory)
+size_t skinny_workspace_bytes(int, int, int) { return 2048 * 8 * 8; }  // (developer time stamps only)
 
 bool skinny_applicable(int M) { return M <= 256; }
 
+struct SkinnyPlan {
+  int stages, tab_cap, smem;
+};
+
+// shared-memory plan: the scale table, the barriers and as many ring stages as fit (two CTAs per SM at M <= 64)
+static SkinnyPlan skinny_plan(int mode, int mt_pad) {
+  SkinnyPlan pl;
+  // (kernels that allocate tensor memory are scheduled one CTA per SM: cudaOccupancyMaxActiveBlocksPerMultiprocessor
+  // answers 1 whatever the shared-memory and register footprint, measured)
+  const int budget = mt_pad <= 64 ? 112 * 1024 : 226 * 1024;
+  const int stage_bytes = SK_BN * SK_BK + mt_pad * SK_BK;
+  const int tab_bytes = mode == 0 ? (mt_pad <= 64 ? 8192 : mt_pad <= 128 ? 16384 : 32768) : 1024;
+  pl.tab_cap = mode == 0 ? tab_bytes / (mt_pad * 4) : 0;
+  int stages = (budget - SK_FIXED_SMEM - tab_bytes) / stage_bytes;
+  if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
+  {
+    static int cap = -1;
+    if (cap < 0) { const char* e = getenv("B200_SK_STAGES"); cap = e ? atoi(e) : 0; }
+    if (cap > 0 && stages > cap) stages = cap;
+  }
+  pl.stages = stages;
+  pl.smem = stages * stage_bytes + SK_FIXED_SMEM + tab_bytes;
+  return pl;
+}
+
 template <int MODE, int COLS, int GROUPS>
-static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyParams& sp, int grid, int smem,
-                           cudaStream_t st) {
+static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, SkinnyParams& sp, int smem, cudaStream_t st) {
   auto kern = gemm_skinny_kernel<MODE, COLS, GROUPS>;
+  constexpr int kThreads = (SK_NONEPI + 4 * GROUPS) * 32;
   static bool configured = false;
+  static int capacity[SK_MAX_SPLITS + 1] = {0};  // CTAs that can be resident at once with clusters of S = 1..8
+  static int capacity_smem = -1;
   if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SK_SMEM_LIMIT));
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3((4 + 4 * GROUPS) * 32);
+  cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = 1;
+  attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  if (capacity_smem != smem) {  // (the plan depends on mt_pad only through smem)
+    for (int S = 1; S <= SK_MAX_SPLITS; ++S) {
+      cfg.gridDim = dim3(1, S);
+      attr[1].val.clusterDim.y = S;
+      cfg.numAttrs = 2;
+      int ncl = 0;
+      B200_CUDA(cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg));
+      // (the occupancy API answers one CTA per SM for kernels that allocate tensor memory; two do co-reside when
+      // registers, shared memory and TMEM columns allow it -- measured -- so the M <= 64 variants count double)
+      capacity[S] = ncl * S * ((COLS * GROUPS <= 64) ? 2 : 1);
+    }
+    capacity_smem = smem;
+  }
+  // K slices per n-tile = cluster size: the S that puts the most CTAs to work while every CTA of (tiles x S) is
+  // resident at once, owns at least two k-blocks, and the exchange buffers fit in the drained ring
+  const int ring_bytes = sp.stages * (SK_BN * SK_BK + sp.mt_pad * SK_BK);
+  const int P = sp.mt_pad < 128 ? sp.mt_pad : 128;
+  int S = 1, best = sp.n_tiles < capacity[1] ? sp.n_tiles : capacity[1];
+  for (int s2 = 2; s2 <= SK_MAX_SPLITS; ++s2) {
+    const int slice = (P + s2 - 1) / s2;
+    const bool fits = (P + (s2 - 1) * slice) * SK_BN * 4 <= ring_bytes;
+    if (sp.n_tiles * s2 <= capacity[s2] && sp.kb_total / s2 >= 2 && fits && sp.n_tiles * s2 > best) {
+      S = s2;
+      best = sp.n_tiles * s2;
+    }
+  }
+  static int force = -1;
+  if (force < 0) { const char* e = getenv("B200_SK_SPLITS"); force = e ? atoi(e) : 0; }
+  if (force > 0 && force <= SK_MAX_SPLITS && sp.kb_total >= force) S = force;
+  sp.splits = S;
+  cfg.gridDim = dim3(sp.n_tiles, S);
+  attr[1].val.clusterDim.y = S;
+  cfg.numAttrs = S > 1 ? 2 : 1;
+  if (sp.debug & 128) {
+    for (int kb = 48; kb <= 116; kb += 4) {
+      int nblk = -1;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nblk, kern, kThreads, kb * 1024);
+      fprintf(stderr, "[skinny] threads %d smem %d KB -> blocks/SM %d\n", kThreads, kb, nblk);
+    }
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, kern);
+    fprintf(stderr, "[skinny] regs %d static smem %zu maxdyn %d carveout %d\n", fa.numRegs, fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, fa.preferredShmemCarveout);
+  }
+  if (sp.debug & 64)
+    fprintf(stderr, "[skinny] M=%d N=%d K=%d tiles=%d S=%d smem=%d stages=%d capacity %d/%d/%d/%d/%d/%d/%d/%d\n", sp.M, sp.N, sp.K,
+            sp.n_tiles, S, smem, sp.stages, capacity[1], capacity[2], capacity[3], capacity[4], capacity[5], capacity[6], capacity[7], capacity[8]);
   B200_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, sp));
+  if (sp.stamps) {
+    static int printed = 0;
+    cudaStreamSynchronize(st);
+    const int n = sp.n_tiles * S;
+    unsigned long long* h = (unsigned long long*)malloc((size_t)n * 64);
+    cudaMemcpy(h, sp.stamps, (size_t)n * 64, cudaMemcpyDeviceToHost);
+    unsigned long long t0 = ~0ULL;
+    for (int c = 0; c < n; ++c) if (h[c * 8] < t0) t0 = h[c * 8];
+    if (printed++ % 8 == 7) {
+      fprintf(stderr, "[skinny stamps] M=%d N=%d K=%d S=%d (ns since first CTA start; min/avg/max over %d CTAs)\n", sp.M, sp.N, sp.K, S, n);
+      for (int i = 0; i < 7; ++i) {
+        unsigned long long mn = ~0ULL, mx = 0, sum = 0;
+        for (int c = 0; c < n; ++c) { unsigned long long v = h[c * 8 + i] - t0; if (v < mn) mn = v; if (v > mx) mx = v; sum += v; }
+        fprintf(stderr, "   stamp %d: %6llu %6llu %6llu\n", i, mn, sum / n, mx);
+      }
+    }
+    free(h);
+  }
   return launched("gemm_skinny_kernel launch");
 }
 
@@ -468,32 +528,27 @@ static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, const S
 template <int MODE>
 int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, SkinnyParams& sp, void* workspace,
                   size_t workspace_bytes, cudaStream_t st) {
+  sp.stamps = nullptr;
   sp.mt_pad = skinny_mt_pad(sp.M);
   sp.n_tiles = (sp.N + SK_BN - 1) / SK_BN;
   sp.kb_total = (sp.K + SK_BK - 1) / SK_BK;
-  sp.units = (long long)sp.n_tiles * sp.kb_total;
-  const int grid = skinny_grid(sp.units);
-  const int stage_bytes = SK_BN * SK_BK + sp.mt_pad * SK_BK;
-  int stages = (SK_SMEM_LIMIT - 1024 - 4096) / stage_bytes;
-  if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
-  sp.stages = stages;
+  const SkinnyPlan pl = skinny_plan(MODE, sp.mt_pad);
+  sp.stages = pl.stages;
+  sp.tab_cap = pl.tab_cap;
   {
     static int dbg = -1;
     if (dbg < 0) { const char* e = getenv("B200_SK_DEBUG"); dbg = e ? atoi(e) : 0; }
     sp.debug = dbg;
+    if ((dbg & 256) && workspace && workspace_bytes >= (size_t)sp.n_tiles * 8 * 64) sp.stamps = (unsigned long long*)workspace;
   }
-  const int smem = stages * stage_bytes + 1024 + 4096;
-  const size_t need = skinny_workspace_bytes(sp.M, sp.N, sp.K);
-  B200_REQUIRE(workspace && workspace_bytes >= need && ((uintptr_t)workspace & 15) == 0, B200_ERR_ARG,
-               "gemm: workspace too small or misaligned (need %zu bytes, have %zu)", need, workspace_bytes);
-  sp.ws_counter = reinterpret_cast<int*>(workspace);
-  sp.ws_partial = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + (((size_t)sp.n_tiles * 4 + 255) & ~(size_t)255));
+  B200_REQUIRE(pl.stages >= 2 && (sp.mt_pad < 128 ? sp.mt_pad : 128) * 512 <= pl.stages * (SK_BN * SK_BK + sp.mt_pad * SK_BK), B200_ERR_UNSUPPORTED,
+               "gemm_skinny: shared-memory plan does not fit (M=%d)", sp.M);
   CUtensorMap tw, tx;
   if (int rc = make_tmap_2d(&tw, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.N, sp.K, ldw, SK_BN, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
   if (int rc = make_tmap_2d(&tx, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.M, sp.K, lda, sp.mt_pad, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
-  if (sp.mt_pad <= 64) return launch_skinny_t<MODE, 64, 1>(tw, tx, sp, grid, smem, st);
-  if (sp.mt_pad <= 128) return launch_skinny_t<MODE, 128, 1>(tw, tx, sp, grid, smem, st);
-  return launch_skinny_t<MODE, 64, 4>(tw, tx, sp, grid, smem, st);
+  if (sp.mt_pad <= 64) return launch_skinny_t<MODE, 32, 2>(tw, tx, sp, pl.smem, st);
+  if (sp.mt_pad <= 128) return launch_skinny_t<MODE, 32, 4>(tw, tx, sp, pl.smem, st);
+  return launch_skinny_t<MODE, 64, 4>(tw, tx, sp, pl.smem, st);
 }
 
 template int launch_skinny<0>(const void*, int64_t, const void*, int64_t, SkinnyParams&, void*, size_t, cudaStream_t);

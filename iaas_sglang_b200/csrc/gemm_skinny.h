@@ -15,11 +15,11 @@ struct SkinnyParams {
   int out_bf16;
   int M, N, K, mt_pad;
   int n_tiles, kb_total;
-  long long units;
-  int stages;
-  int debug;  // developer knobs (B200_SK_DEBUG): 1 = skip the split-tile fix-up, 2 = skip the fp8 promotion
-  float* ws_partial;  // [grid][2][mt_pad][128] fp32 (int32 bits in MODE 1)
-  int* ws_counter;    // [n_tiles] tickets, zero on entry, self-resetting
+  int splits;   // CTAs per cluster = K slices per n-tile (1, 2, 4 or 8)
+  int stages;   // depth of the TMA ring
+  int tab_cap;  // MODE 0: k-blocks per chunk of the shared-memory scale table
+  unsigned long long* stamps;  // developer: per-CTA %globaltimer stamps (B200_SK_DEBUG & 256)
+  int debug;    // developer knobs (B200_SK_DEBUG): 1 skip the DSMEM scatter, 2 skip the whole exchange, 4 skip the final sum
 };
 
 size_t skinny_workspace_bytes(int M, int N, int K);

@@ -25,6 +25,11 @@
 
 namespace b200 {
 
+// gemm_big.cu: persistent 256-wide-tile kernel for M > 256 (mode 0 fp8 block-scaled, 1 int8)
+int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw, const float* sa, int64_t sa_sm, int64_t sa_sk,
+               const float* sb, int64_t sb_sk, int64_t sb_sn, const void* bias, void* out, int64_t ldo, int out_bf16, int M,
+               int N, int K, cudaStream_t st);
+
 constexpr int BM = 128, BN = 128, BKB = 128;  // BKB: bytes (== elements) of K per stage
 constexpr int kStages = 6;
 constexpr int kStageBytes = (BM + BN) * BKB;  // 32 KB
@@ -374,12 +379,8 @@ extern "C" int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const vo
     sp.M = M; sp.N = N; sp.K = K;
     return launch_skinny<0>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
   }
-  GemmParams gp{};
-  gp.sa = sa; gp.sa_sm = sa_sm; gp.sa_sk = sa_sk;
-  gp.sb = sb; gp.sb_sk = sb_sk; gp.sb_sn = sb_sn;
-  gp.bias = nullptr; gp.out = out; gp.ldo = ldo; gp.out_bf16 = out_dtype == B200_BF16;
-  gp.M = M; gp.N = N; gp.K = K;
-  return launch_gemm<0>(a, lda, b, ldb, gp, workspace, workspace_bytes, (cudaStream_t)stream);
+  return launch_big(0, a, lda, b, ldb, sa, sa_sm, sa_sk, sb, sb_sk, sb_sn, nullptr, out, ldo, out_dtype == B200_BF16, M, N, K,
+                    (cudaStream_t)stream);
 }
 
 namespace b200 {
@@ -418,8 +419,5 @@ extern "C" int b200_int8_scaled_mm(const void* a, int64_t lda, const void* b, in
     sp.M = M; sp.N = N; sp.K = K;
     return launch_skinny<1>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
   }
-  GemmParams gp{};
-  gp.sa = sa; gp.sb = sb; gp.bias = bias; gp.out = out; gp.ldo = ldo; gp.out_bf16 = out_dtype == B200_BF16;
-  gp.M = M; gp.N = N; gp.K = K;
-  return launch_gemm<1>(a, lda, b, ldb, gp, workspace, workspace_bytes, (cudaStream_t)stream);
+  return launch_big(1, a, lda, b, ldb, sa, 0, 0, sb, 0, 0, bias, out, ldo, out_dtype == B200_BF16, M, N, K, (cudaStream_t)stream);
 }

@@ -236,6 +236,22 @@ def bench_profgemm():
     fp8_case(64, 6144, 4096)
 
 
+def bench_profbig():
+    """a few plain launches of the large-M fp8 GEMM for ncu (-k regex:gemm_big)"""
+    global timeit
+
+    def timeit(fn, n_variants, reps=0, warm=3):  # noqa: F811
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn(0); fn(1 % n_variants)
+        e0.record()
+        fn(0); fn(1 % n_variants)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 2
+
+    fp8_case(4096, 8192, 8192, 2 * BF16_TF)
+
+
 def main():
     what = sys.argv[1:] or ["attn", "gemm", "gemm_big", "int8", "awq"]
     print(f"# peaks: HBM {HBM} GB/s, bf16 {BF16_TF} TFLOP/s (MEASURED_PEAKS.json or fallback)")

@@ -23,6 +23,7 @@ FLAGS = [
 ]
 FLAGS = [f for f in FLAGS if f != "--use_fast_math_off_placeholder"]
 FLAGS += ["-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+FLAGS += os.environ.get("B200_NVCC_EXTRA", "").split()
 
 
 def sources():

@@ -20,6 +20,7 @@
 //   works on the next k-block (each warp: 32 rows x 64 columns).
 //   INT8: int32 accumulation stays in TMEM for the whole K loop (exact); the two buffers alternate between tiles,
 //   so the epilogue of tile i overlaps the main loop of tile i+1.
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -27,10 +28,8 @@
 namespace b200 {
 
 constexpr int GB_BM = 128;   // rows of A per CTA
-constexpr int GB_BN = 256;   // output columns per tile (UMMA N)
 constexpr int GB_BK = 128;   // bytes of K per k-block
-constexpr int GB_EPI_WARPS = 16;
-constexpr int GB_THREADS = (4 + GB_EPI_WARPS) * 32;
+// BN = output columns per tile (UMMA N): 256 (two TMEM buffers) or 128 (four); 4 * BN / 64 epilogue warps
 constexpr int GB_MAX_STAGES = 8;
 
 struct BigParams {
@@ -44,6 +43,7 @@ struct BigParams {
   int out_bf16;
   int M, N, K;
   int kb_total, tiles_m, tiles_n, n_tiles, group_m, workers;
+  long long* prof;  // developer (B200_GB_PROF=1): per-CTA clock64 sums of the pipeline waits
 };
 
 // ---- cluster / cta_group::2 helpers ----
@@ -124,6 +124,11 @@ __device__ __forceinline__ void gb_ld_wait32(uint32_t (&r)[32]) {
                  "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])::"memory");
 }
 __device__ __forceinline__ void gb_fma2(float2& acc, uint32_t x0, uint32_t x1, float s) {
+#ifdef GB_PLAIN_FMA
+  acc.x = fmaf(__uint_as_float(x0), s, acc.x);
+  acc.y = fmaf(__uint_as_float(x1), s, acc.y);
+  return;
+#endif
   uint64_t x, sc;
   asm("mov.b64 %0, {%1, %2};" : "=l"(x) : "r"(x0), "r"(x1));
   asm("mov.b64 %0, {%1, %1};" : "=l"(sc) : "f"(s));
@@ -140,13 +145,14 @@ __device__ __forceinline__ void gb_tile_coord(const BigParams& p, int t, int& tm
   tm = first_m + (r - tn * gm);
 }
 
-template <int MODE, int PAIR>
-__global__ void __launch_bounds__(GB_THREADS, 1)
+template <int MODE, int PAIR, int BN>
+__global__ void __launch_bounds__((4 + BN / 16) * 32, 1)
 gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                 const __grid_constant__ BigParams p, const int stages) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   constexpr int A_BYTES = GB_BM * GB_BK;                   // 16 KB
+  constexpr int GB_BN = BN, GB_EPI_WARPS = BN / 16, NBUF = 512 / BN;
   constexpr int B_ROWS = GB_BN / PAIR;                     // W rows staged by this CTA
   constexpr int B_BYTES = B_ROWS * GB_BK;                  // 32 KB / 16 KB
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -154,8 +160,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
   uint64_t* empty = full + GB_MAX_STAGES;
   uint64_t* tfull = empty + GB_MAX_STAGES;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* tempty = tfull + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = PAIR == 2 ? (int)gb_cluster_rank() : 0;
@@ -171,7 +177,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < NBUF; ++a) {
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], GB_EPI_WARPS * PAIR);
     }
@@ -214,15 +220,24 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     const uint32_t idesc = MODE == 0 ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, GB_BM * PAIR, GB_BN)
                                      : umma_idesc(2 /*s32*/, 1 /*s8*/, 1, GB_BM * PAIR, GB_BN);
     int it = 0, tile_it = 0;
+    long long pm_tempty = 0, pm_full = 0;
+    const long long pm_t0 = clock64();
     for (int t = worker; t < p.n_tiles; t += p.workers, ++tile_it) {
       for (int kb = 0; kb < p.kb_total; ++kb, ++it) {
         const int s = it % stages;
         const uint32_t ph = (it / stages) & 1;
-        const int a = MODE == 0 ? (it & 1) : (tile_it & 1);
-        if (MODE == 0) mbar_wait(&tempty[a], ((it >> 1) & 1) ^ 1);
-        else if (kb == 0) mbar_wait(&tempty[a], ((tile_it >> 1) & 1) ^ 1);
+        const int a = MODE == 0 ? (it % NBUF) : (tile_it % NBUF);
+        const long long c0 = p.prof ? clock64() : 0;
+        if (MODE == 0) mbar_wait(&tempty[a], ((it / NBUF) & 1) ^ 1);
+        else if (kb == 0) mbar_wait(&tempty[a], ((tile_it / NBUF) & 1) ^ 1);
+        const long long c1 = p.prof ? clock64() : 0;
         mbar_wait(&full[s], ph);
         tc_fence_after();
+        if (p.prof) {
+          const long long c2 = clock64();
+          pm_tempty += c1 - c0;
+          pm_full += c2 - c1;
+        }
         const uint32_t a_addr = smem_u32(smem + s * STAGE_BYTES);
         const uint64_t adesc = umma_desc_k_sw128(a_addr);
         const uint64_t bdesc = umma_desc_k_sw128(a_addr + A_BYTES);
@@ -235,6 +250,12 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         gb_commit<PAIR>(&empty[s]);
         if (MODE == 0 || kb == p.kb_total - 1) gb_commit<PAIR>(&tfull[a]);
       }
+    }
+    if (p.prof) {
+      p.prof[blockIdx.x * 8 + 0] = clock64() - pm_t0;
+      p.prof[blockIdx.x * 8 + 1] = pm_tempty;
+      p.prof[blockIdx.x * 8 + 2] = pm_full;
+      p.prof[blockIdx.x * 8 + 3] = it;
     }
   } else if (warp >= 4) {
     // ================================ epilogue warps ================================
@@ -251,6 +272,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       }
     };
     int it = 0, tile_it = 0;
+    long long pe_wait = 0, pe_ld = 0;
+    const long long pe_t0 = clock64();
     for (int t = worker; t < p.n_tiles; t += p.workers, ++tile_it) {
       int tm, tn;
       gb_tile_coord(p, t, tm, tn);
@@ -277,20 +300,38 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           for (int d = 0; d < 4; ++d) {
             const int kb = kbq + d;
             if (kb < p.kb_total) {
-              const int a = it & 1;
+              const int a = it % NBUF;
               const float sc = saq[d] * sbq[d];
               if (kb + 4 < p.kb_total) {
                 saq[d] = load_sa(kb + 4);
                 sbq[d] = load_sb(kb + 4);
               }
-              mbar_wait(&tfull[a], (it >> 1) & 1);
+#ifdef GB_PROF_EPI
+              const long long e0 = p.prof ? clock64() : 0;
+#endif
+              mbar_wait(&tfull[a], (it / NBUF) & 1);
               tc_fence_after();
+#ifdef GB_PROF_EPI
+              const long long e1 = p.prof ? clock64() : 0;
+#endif
               uint32_t r0[32], r1[32];
+#ifdef GB_SKIP_LD
+#pragma unroll
+              for (int j = 0; j < 32; ++j) r0[j] = r1[j] = (uint32_t)(it + j);
+#else
               tmem_ld_32x32(lane_addr + a * GB_BN, r0);
               tmem_ld_32x32(lane_addr + a * GB_BN + 32, r1);
               gb_ld_wait32(r0);
               gb_ld_wait32(r1);
+#endif
               release(a);
+#ifdef GB_PROF_EPI
+              if (p.prof) {
+                const long long e2 = clock64();
+                pe_wait += e1 - e0;
+                pe_ld += e2 - e1;
+              }
+#endif
 #pragma unroll
               for (int j = 0; j < 16; ++j) gb_fma2(acc[j], r0[2 * j], r0[2 * j + 1], sc);
 #pragma unroll
@@ -300,8 +341,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           }
         }
       } else {
-        const int a = tile_it & 1;
-        mbar_wait(&tfull[a], (tile_it >> 1) & 1);
+        const int a = tile_it % NBUF;
+        mbar_wait(&tfull[a], (tile_it / NBUF) & 1);
         tc_fence_after();
         uint32_t r0[32], r1[32];
         tmem_ld_32x32(lane_addr + a * GB_BN, r0);
@@ -350,6 +391,11 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           }
         }
       }
+      if (p.prof && threadIdx.x == 128 && t + p.workers >= p.n_tiles) {
+        p.prof[blockIdx.x * 8 + 4] = clock64() - pe_t0;
+        p.prof[blockIdx.x * 8 + 5] = pe_wait;
+        p.prof[blockIdx.x * 8 + 6] = pe_ld;
+      }
     }
   }
 
@@ -362,8 +408,9 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   }
 }
 
-template <int MODE, int PAIR>
+template <int MODE, int PAIR, int BN>
 static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, BigParams& bp, cudaStream_t st) {
+  constexpr int GB_BN = BN, GB_THREADS = (4 + BN / 16) * 32;
   constexpr int STAGE_BYTES = GB_BM * GB_BK + (GB_BN / PAIR) * GB_BK;
   const int stages = (226 * 1024 - 1024 - 512) / STAGE_BYTES > GB_MAX_STAGES ? GB_MAX_STAGES : (226 * 1024 - 1024 - 512) / STAGE_BYTES;
   const int smem = stages * STAGE_BYTES + 1024 + 512;
@@ -379,7 +426,7 @@ static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, 
   CUtensorMap ta, tb;
   if (int rc = make_tmap_2d(&ta, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, bp.M, bp.K, lda, GB_BM, GB_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
   if (int rc = make_tmap_2d(&tb, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, bp.N, bp.K, ldw, GB_BN / PAIR, GB_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
-  auto kern = gemm_big_kernel<MODE, PAIR>;
+  auto kern = gemm_big_kernel<MODE, PAIR, BN>;
   static bool configured = false;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -397,7 +444,24 @@ static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = PAIR > 1 ? 1 : 0;
+  static int prof = -1;
+  static long long* dprof = nullptr;
+  if (prof < 0) { const char* e = getenv("B200_GB_PROF"); prof = e ? atoi(e) : 0; if (prof) cudaMalloc(&dprof, 160 * 64); }
+  bp.prof = prof ? dprof : nullptr;
   B200_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, bp, stages));
+  if (prof) {
+    static int n = 0;
+    cudaStreamSynchronize(st);
+    long long h[160 * 8];
+    cudaMemcpy(h, dprof, sizeof(h), cudaMemcpyDeviceToHost);
+    if (n++ % 8 == 3) {
+      double s[8] = {0};
+      const int g = workers * PAIR;
+      for (int c = 0; c < g; ++c) for (int i = 0; i < 8; ++i) s[i] += (double)h[c * 8 + i] / g;
+      fprintf(stderr, "[gemm_big prof] M=%d N=%d K=%d BN=%d: MMA thread total %.0f cyc, wait tempty %.0f, wait full %.0f, k-blocks %.0f | epi warp total %.0f, wait tfull %.0f, ld+release %.0f\n",
+              bp.M, bp.N, bp.K, BN, s[0], s[1], s[2], s[3], s[4], s[5], s[6]);
+    }
+  }
   return launched("gemm_big_kernel launch");
 }
 
@@ -411,11 +475,20 @@ int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw,
   bp.bias = bias; bp.out = out; bp.ldo = ldo; bp.out_bf16 = out_bf16;
   bp.M = M; bp.N = N; bp.K = K;
   static int pair = -1;
-  if (pair < 0) { const char* e = getenv("B200_GB_PAIR"); pair = e ? atoi(e) : 1; }
-  if (pair == 2 && M > GB_BM) {
-    return mode == 0 ? launch_big_t<0, 2>(a, lda, w, ldw, bp, st) : launch_big_t<1, 2>(a, lda, w, ldw, bp, st);
+  if (pair < 0) { const char* e = getenv("B200_GB_PAIR"); pair = e ? atoi(e) : 2; }
+  static int bn = -1;
+  if (bn < 0) { const char* e = getenv("B200_GB_BN"); bn = e ? atoi(e) : 128; }
+  if (mode == 0) {
+    // fp8: the per-k-block TMEM hand-shake with remote CTAs is too slow for pairs (464 vs 1190 TFLOP/s measured).
+    // 128-wide tiles have four TMEM buffers, so the tensor core never waits for the promotion (the MMA thread is then
+    // issue-bound: a 128x128x32 instruction costs the same ~175 cycles as a 128x256x32 one); 256-wide tiles have two
+    // buffers and wait ~980 cycles per k-block for the promotion, whose tcgen05.ld shares the TMEM port with the
+    // running MMA (tools/gb_prof.py).  1.25 vs 1.19 PFLOP/s.
+    if (bn == 128) return launch_big_t<0, 1, 128>(a, lda, w, ldw, bp, st);
+    return launch_big_t<0, 1, 256>(a, lda, w, ldw, bp, st);
   }
-  return mode == 0 ? launch_big_t<0, 1>(a, lda, w, ldw, bp, st) : launch_big_t<1, 1>(a, lda, w, ldw, bp, st);
+  if (pair != 1 && M > GB_BM) return launch_big_t<1, 2, 256>(a, lda, w, ldw, bp, st);
+  return launch_big_t<1, 1, 256>(a, lda, w, ldw, bp, st);
 }
 
 }  // namespace b200

@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 SO = os.path.join(HERE, "libb200sgl.so")
 SOURCES = ["runtime.cu", "elementwise.cu", "decode_attn.cu", "extend_attn.cu", "gemm_tc.cu", "gemm_skinny.cu", "gemm_big.cu", "awq_gemm.cu"]
-HEADERS = ["common.cuh", "gemm_skinny.h", os.path.join(ROOT, "include", "b200_sgl.h")]
+HEADERS = ["common.cuh", "gemm_skinny.h", "decode_mla.cuh", os.path.join(ROOT, "include", "b200_sgl.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--use_fast_math_off_placeholder",

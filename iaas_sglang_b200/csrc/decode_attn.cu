@@ -817,6 +817,8 @@ static int launch_generic(const DecodeKParams& kp, cudaStream_t st) {
   return launched("decode_attn_generic_kernel launch");
 }
 
+#include "decode_mla.cuh"
+
 }  // namespace b200
 
 using namespace b200;
@@ -825,6 +827,7 @@ extern "C" int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv
   if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv != 0) return 1;
   // tuned path: the KV work is partitioned on the device from the actual seq_lens (no fixed split count)
   if (mma_path_ok(Hq, Hkv, D, Dv)) return 1;
+  if (Hkv == 1 && D == MlaCfg::D && Dv == MlaCfg::Dv && num_splits_hint <= 1) return 1;  // tuned MLA path
   // generic path: 128-thread CTAs, many per SM -> aim for >= 8 CTAs per SM
   if (num_splits_hint > 0) return num_splits_hint > 64 ? 64 : num_splits_hint;
   if (max_seq_len <= 0) max_seq_len = 4096;
@@ -839,7 +842,7 @@ extern "C" int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv
 }
 
 extern "C" size_t b200_decode_attn_workspace_size(int B, int Hq, int Dv, int num_splits) {
-  const size_t tuned = (Dv == 64 || Dv == 128) ? mma_workspace_bytes(Dv) : 16;
+  const size_t tuned = (Dv == 64 || Dv == 128) ? mma_workspace_bytes(Dv) : (Dv == MlaCfg::Dv ? mla_workspace_bytes() : 16);
   const size_t generic = num_splits <= 1 ? 16 : ((size_t)B * Hq * num_splits * (Dv + 1)) * sizeof(float) + 256;
   return tuned > generic ? tuned : generic;
 }
@@ -899,8 +902,19 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
     if (!rows_ok || !q_ok) mma = false;
     if (mma && hpc > 1 && (a->kbuf_stride_h != a->D || a->vbuf_stride_h != a->Dv)) hpc = 1;  // heads not adjacent
   }
+  // tuned MLA path (decode_mla.cuh): 16-byte aligned latent rows, 4-byte aligned q rows; an explicit split-count
+  // hint selects the generic kernel (the tuned kernel partitions the KV work itself)
+  bool mla = mla_path_ok(a->Hkv, a->D, a->Dv, is_mla) && a->num_splits <= 1;
+  if (mla) {
+    const bool rows_ok = ((uintptr_t)a->k_buf & 15) == 0 && a->kbuf_stride_t % 8 == 0;
+    const bool q_ok = ((uintptr_t)a->q & 3) == 0 && a->q_stride_b % 2 == 0 && a->q_stride_h % 2 == 0;
+    if (!rows_ok || !q_ok) mla = false;
+  }
   // fused append (write_kv == 2) needs aligned, head-contiguous new rows on the tuned path
   bool fused = (write_kv == 2);
+  if (fused && mla) {
+    if (((uintptr_t)a->k_new & 15) != 0 || a->knew_stride_b % 8 != 0) fused = false;
+  }
   if (fused && mma) {
     auto al16 = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
     const bool new_ok = al16(a->k_new) && al16(a->v_new) && a->knew_stride_b % 8 == 0 && a->vnew_stride_b % 8 == 0 &&
@@ -917,6 +931,27 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
   }
   kp.fused_new = fused ? 1 : 0;
 
+  if (mla && !mma) {
+    const size_t need = mla_workspace_bytes();
+    B200_REQUIRE(a->workspace && a->workspace_bytes >= need && ((uintptr_t)a->workspace & 15) == 0, B200_ERR_ARG,
+                 "decode_attn: workspace too small or misaligned (need %zu bytes, have %zu)", need, a->workspace_bytes);
+    kp.num_splits = 1;
+    kp.part_o = (float*)a->workspace;
+    kp.part_lse = kp.part_o + (size_t)attn_grid() * 2 * 16 * a->Dv;
+    for (int b0 = 0; b0 < a->B; b0 += kMaxBatchTable) {
+      DecodeKParams c = kp;
+      c.B = a->B - b0 < kMaxBatchTable ? a->B - b0 : kMaxBatchTable;
+      c.q = kp.q + (int64_t)b0 * kp.q_sb;
+      if (kp.k_new) c.k_new = kp.k_new + (int64_t)b0 * kp.kn_sb;
+      c.out = kp.out + (int64_t)b0 * kp.Hq * kp.Dv;
+      c.rpi = kp.rpi + b0;
+      c.seq_lens = kp.seq_lens + b0;
+      if (kp.loc) c.loc = kp.loc + b0;
+      const int rc = a->dtype == B200_BF16 ? launch_mla<true>(c, st) : launch_mla<false>(c, st);
+      if (rc != 0) return rc;
+    }
+    return B200_OK;
+  }
   if (mma) {
     const size_t need = mma_workspace_bytes(a->Dv);
     B200_REQUIRE(a->workspace && a->workspace_bytes >= need && ((uintptr_t)a->workspace & 15) == 0, B200_ERR_ARG,

@@ -192,3 +192,62 @@ def test_baseline_config_shapes(cfg):
     assert torch.equal(out2, out * 2)
     # (d) appended rows landed exactly
     assert torch.equal(d["k_buf"][d["loc"]], d["k_new"]) and torch.equal(d["v_buf"][d["loc"]], d["v_new"])
+
+
+# ---- MLA absorbed decode, tuned kernel (decode_mla.cuh): 16-head q blocks over 64-token tiles ----
+@pytest.mark.parametrize("seq_lens", [[1], [1, 2, 3, 17], [63, 64, 65, 31, 32, 33], [128, 129, 127, 1], [5000, 3, 977],
+                                      [2048] * 5])
+@pytest.mark.parametrize("Hq", [16, 22, 5, 128])
+def test_mla_ragged_lengths_and_head_counts(seq_lens, Hq):
+    check(DecodeCase(len(seq_lens), Hq, 1, 576, 512, seq_lens), fused=True)
+    check(DecodeCase(len(seq_lens), Hq, 1, 576, 512, seq_lens), fused=False)
+
+
+def test_mla_fp16_no_write_and_padding_rows():
+    c = DecodeCase(3, 16, 1, 576, 512, [700, 64, 9], dtype=torch.float16)
+    ref, _, _ = c.oracle(round_p=False)
+    out, _, _ = run_cuda_decode(c, fused=True)
+    assert rel_l2(out, ref) < 5e-4
+    check(DecodeCase(2, 16, 1, 576, 512, 300), write_kv=False)
+    c = DecodeCase(4, 16, 1, 576, 512, [300, 1, 1, 1])
+    c.req_pool_indices[1:] = 0
+    c.loc[1:] = 0
+    check(c, first_slot=1, fused=True)
+
+
+def test_mla_tuned_kernel_matches_generic_kernel_and_many_ctas_per_request():
+    """One long request is split over all 148 CTAs (partials + merge); the generic kernel (explicit split count) is
+    an independent implementation of the same op."""
+    c = DecodeCase(2, 16, 1, 576, 512, [40000, 150])
+    a, _, _ = run_cuda_decode(c, fused=True)
+    b, _, _ = run_cuda_decode(c, fused=True, num_splits=16)
+    assert rel_l2(a, b) < 1e-3
+
+
+def test_mla_cfg5_tp8_slice_properties():
+    """BASELINE config 5 per-GPU shape (16 heads, latent 576/512) on a slice of the batch: oracle on a sample,
+    exact linearity in the latent's value part, exact append."""
+    from iaas_sglang_b200 import ops
+
+    B, Hq, S = 24, 16, 16384
+    c = DecodeCase(B, Hq, 1, 576, 512, S)
+    d = c.cuda()
+    out = torch.zeros(B, Hq, 512, dtype=torch.bfloat16, device="cuda")
+    tail = (d["loc"], None, d["req_to_token"], d["req_pool_indices"], d["seq_lens"], c.sm_scale, 0.0)
+    ops.decode_attention(d["q"], d["k_buf"], d["v_buf"], out, d["k_new"], d["v_new"], *tail, max_seq_len=S,
+                         fused_kv_write=True)
+    sample = [0, B // 2, B - 1]
+    sub = DecodeCase.__new__(DecodeCase)
+    sub.__dict__.update(c.__dict__)
+    sub.B = len(sample)
+    sub.q, sub.k_new, sub.v_new = c.q[sample], c.k_new[sample], c.v_new[sample]
+    sub.req_pool_indices, sub.seq_lens, sub.loc = c.req_pool_indices[sample], c.seq_lens[sample], c.loc[sample]
+    ref, _, _ = sub.oracle(round_p=False)
+    assert rel_l2(out[sample].cpu(), ref) < TOL
+    assert torch.equal(d["k_buf"][d["loc"]], d["k_new"])
+    # scaling the value columns (first 512) by 2 would also change the keys, so scale a copy used as V only: the
+    # generic kernel accepts distinct K and V pools and must agree with the tuned one
+    out_g = torch.zeros_like(out)
+    ops.decode_attention(d["q"], d["k_buf"], d["v_buf"], out_g, None, None, None, None, *tail[2:], max_seq_len=S,
+                         num_splits=8)
+    assert rel_l2(out_g, out) < 1e-3

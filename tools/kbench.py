@@ -252,6 +252,48 @@ def bench_profbig():
     fp8_case(4096, 8192, 8192, 2 * BF16_TF)
 
 
+def mla_case(name, B, Hq, ctx, layers=2, var=False, splits=0):
+    """MLA absorbed decode: latent pool [T, 1, 576], V = first 512 columns (cutlass_mla_decode's shapes, cfg 5)."""
+    g = torch.Generator(device=DEV).manual_seed(1234)
+    D, Dv = 576, 512
+    unique = B * ctx
+    perm = torch.randperm(unique, device=DEV, generator=g) + 1
+    r2t = perm.view(B, ctx).to(torch.int32)
+    if var:
+        seq = torch.randint(ctx // 2, ctx + 1, (B,), device=DEV, generator=g, dtype=torch.int64)
+    else:
+        seq = torch.full((B,), ctx, dtype=torch.int64, device=DEV)
+    rpi = torch.arange(B, dtype=torch.int64, device=DEV)
+    loc = r2t.gather(1, (seq - 1)[:, None]).view(-1).to(torch.int64)
+    kbufs = [torch.randn(unique + 1, 1, D, device=DEV, dtype=torch.bfloat16, generator=g) for _ in range(layers)]
+    q = torch.randn(B, Hq, D, device=DEV, dtype=torch.bfloat16, generator=g)
+    k = torch.randn(B, 1, D, device=DEV, dtype=torch.bfloat16, generator=g)
+    o = torch.empty(B, Hq, Dv, device=DEV, dtype=torch.bfloat16)
+    S = ops.decode_attention_num_splits(B, Hq, 1, D, Dv, ctx, splits)
+    ws = torch.empty(ops.decode_attention_workspace_bytes(B, Hq, Dv, S), dtype=torch.uint8, device=DEV)
+
+    def run(i):
+        ops.decode_attention(q, kbufs[i], kbufs[i].narrow(2, 0, Dv), o, k, k.narrow(2, 0, Dv), loc, ws, r2t, rpi, seq,
+                             D ** -0.5, 0.0, max_seq_len=ctx, fused_kv_write=True, num_splits=splits)
+
+    ms = timeit(run, layers, reps=10)
+    tot = int(seq.sum())
+    nbytes = tot * D * 2 + tot * 4 + B * Hq * (D + Dv) * 2 + B * D * 2 * 2
+    report(f"mla {name} B{B} H{Hq} ctx{ctx} S{S}" + (" var" if var else "") + (" generic" if splits else ""), ms, nbytes,
+           2 * tot * Hq * (D + Dv))
+    del kbufs
+    torch.cuda.empty_cache()
+
+
+def bench_mla():
+    mla_case("cfg5tp8", 256, 16, 16384)
+    mla_case("cfg5tp8", 256, 16, 16384, var=True)
+    mla_case("cfg5tp8-small", 64, 16, 4096, layers=4)
+    mla_case("tp4", 64, 32, 8192)
+    mla_case("tp1", 16, 128, 8192)
+    mla_case("cfg5tp8-small", 64, 16, 4096, layers=4, splits=8)
+
+
 def main():
     what = sys.argv[1:] or ["attn", "gemm", "gemm_big", "int8", "awq"]
     print(f"# peaks: HBM {HBM} GB/s, bf16 {BF16_TF} TFLOP/s (MEASURED_PEAKS.json or fallback)")

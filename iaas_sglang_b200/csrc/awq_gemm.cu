@@ -1,11 +1,13 @@
 // AWQ INT4 W4A16 linear: python/sglang/srt/layers/quantization/awq.py:186-204
 //   out = x @ awq_dequantize(qweight, scales, qzeros) (+ bias)
-// v1 keeps the reference's two-phase structure but entirely in our own sm_100a kernels and in the
+// Decode shapes (M <= 256, K % 64 == 0, N % 32 == 0): ONE fused kernel, gemm_skinny_kernel<MODE 2> (gemm_skinny.cu):
+// the packed int4 tile is dequantised in registers into the tcgen05 operand tile, 0.5 B of HBM traffic per weight.
+// Other shapes keep the reference's two-phase structure, entirely in our own sm_100a kernels and in the
 // layout the tcgen05 GEMM wants: the weight is dequantised TRANSPOSED into a K-major [N, K] half
 // buffer in the caller's workspace (so both GEMM operands are K-major / SWIZZLE_128B TMA tiles),
 // then gemm_tc_kernel<MODE 2> (tcgen05.mma kind::f16, fp32 accumulate in TMEM) does x . W^T.
 // The dequantised values are bit-identical to awq_dequantize (awq_kernel.cu:126-221).
-#include "common.cuh"
+#include "gemm_skinny.h"
 
 namespace b200 {
 
@@ -52,6 +54,8 @@ __global__ void __launch_bounds__(256) awq_dequant_t_kernel(const int32_t* __res
   }
 }
 
+static bool awq_fused_shape(int M, int N, int K) { return skinny_applicable(M) && K % 64 == 0 && N % 32 == 0; }
+
 }  // namespace b200
 
 using namespace b200;
@@ -66,12 +70,20 @@ extern "C" int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qwei
   if (M == 0) return B200_OK;
   const int arch = b200_sm_arch();
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "awq_w4a16_mm: requires an sm_100 device (got sm_%d); no fallback", arch);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (awq_fused_shape(M, N, K) && group % 8 == 0 && ldx % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)qweight & 15) == 0 &&
+      ((uintptr_t)scales & 15) == 0) {
+    SkinnyParams sp{};
+    sp.bias = bias; sp.out = out; sp.ldo = ldo; sp.out_bf16 = dtype == B200_BF16;
+    sp.qzeros = qzeros; sp.scales = (const uint16_t*)scales; sp.group = group;
+    sp.M = M; sp.N = N; sp.K = K;
+    return launch_skinny<2>(x, ldx * 2, qweight, (int64_t)N / 2, sp, workspace, workspace_bytes, st);
+  }
   const size_t wt_bytes = ((size_t)N * K * 2 + 255) & ~(size_t)255;
   const size_t gemm_ws = (dense_half_gemm_workspace(M, N, K) + 255) & ~(size_t)255;
   B200_REQUIRE(workspace && workspace_bytes >= wt_bytes + gemm_ws && ((uintptr_t)workspace & 255) == 0, B200_ERR_ARG,
                "awq_w4a16_mm: workspace too small or not 256-byte aligned (need %zu bytes, have %zu)", wt_bytes + gemm_ws,
                workspace_bytes);
-  cudaStream_t st = (cudaStream_t)stream;
   // the split-K ticket counters live at the START of the workspace (zeroed once by the caller)
   uint8_t* gemm_ws_ptr = reinterpret_cast<uint8_t*>(workspace);
   uint16_t* wt = reinterpret_cast<uint16_t*>(gemm_ws_ptr + gemm_ws);
@@ -87,6 +99,9 @@ extern "C" int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qwei
 
 extern "C" size_t b200_awq_w4a16_workspace_size(int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 256;
+  // (the fused path needs none; a call that cannot take it -- unaligned operands, group % 8 != 0 -- is told so by the
+  // workspace check of b200_awq_w4a16_mm)
+  if (awq_fused_shape(M, N, K)) return (skinny_workspace_bytes(M, N, K) + 255) & ~(size_t)255;
   const size_t wt_bytes = ((size_t)N * K * 2 + 255) & ~(size_t)255;
   return ((dense_half_gemm_workspace(M, N, K) + 255) & ~(size_t)255) + wt_bytes;
 }

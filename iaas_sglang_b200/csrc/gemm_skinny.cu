@@ -2,6 +2,9 @@
 //
 //   MODE 0  fp8_blockwise_scaled_mm  (sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:345-423)
 //   MODE 1  int8_scaled_mm           (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747)
+//   MODE 2  AWQ W4A16 linear         (python/sglang/srt/layers/quantization/awq.py:186-204 = awq_dequantize,
+//           sgl-kernel/csrc/gemm/awq_kernel.cu:126-221, followed by a half GEMM) fused: the packed int4 tile is the
+//           only weight traffic (0.5 B per weight instead of 4.5 B through a dequantised copy)
 //
 // At decode M (64..256 tokens) these GEMMs stream the weight once and are bound by HBM, not by the tensor
 // core, so the kernel is built to keep the copy engine busy on every SM and to keep everything else short:
@@ -22,6 +25,11 @@
 //     products of the CTA's K range are tabulated in shared memory once, so the k-loop has no global loads and
 //     no CTA barriers;
 //   INT8: int32 accumulation in TMEM over the CTA's K range (exact), integer reduce-scatter, scales at the end.
+//   AWQ: TMA brings the raw [64 k x 16 words] int4 box (4 KB) and the activation tile; the epilogue warps, idle during
+//     the k-loop, are the dequantisers: group g takes every GROUPS-th stage, a thread turns 8 k-rows x one packed word
+//     into eight 16-byte K-major chunks ((nib | magic) - (zero | magic)) * scale in half2 -- the values awq_dequantize
+//     produces, bit for bit -- and stores them into the SWIZZLE_128B operand tile (UMMA row i holds column
+//     n = 8 (i % 16) + i / 16 of the tile, which makes the stores bank-conflict free); fp32 accumulation in TMEM.
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -71,6 +79,76 @@ __device__ __forceinline__ void sk_epi_bar_all() {
   asm volatile("bar.sync 1, %0;" ::"n"(GROUPS * 128) : "memory");
 }
 
+// MODE 2: dequantise the raw int4 boxes of stages grp, grp + GROUPS, ... into the K-major SWIZZLE_128B operand tile.
+// `row` = thread index inside its 128-thread group: packed word column c = row % 16, k-octet ko = row / 16.
+template <bool BF, int GROUPS>
+__device__ __forceinline__ void awq_dequant_stages(const SkinnyParams& p, uint8_t* smem, uint64_t* full, uint64_t* afull,
+                                                   int stage_bytes, int x_bytes, int tile, int kb0, int nkb, int rot,
+                                                   int grp, int row) {
+  const int c = row & 15, ko = row >> 4, h = ko & 1;
+  constexpr uint32_t magic = BF ? 0x43004300u : 0x64006400u;  // 128 + nibble (bf16) / 1024 + nibble (f16), exact
+  const int ncol = tile * 16 + c;
+  const bool col_ok = ncol * 8 < p.N;
+  int cur_g = -1;
+  uint32_t zp[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
+  for (int i = grp; i < nkb; i += GROUPS) {
+    const int s = i % p.stages;
+    const uint32_t ph = (i / p.stages) & 1;
+    const int kb = kb0 + (i + rot >= nkb ? i + rot - nkb : i + rot);
+    const int gi = (kb * 64 + ko * 8) / p.group;  // a thread's 8 k-rows share a group (group % 8 == 0)
+    if (gi != cur_g) {
+      cur_g = gi;
+      uint4 sraw = make_uint4(0u, 0u, 0u, 0u);
+      uint32_t z = 0;
+      if (col_ok) {
+        sraw = __ldg(reinterpret_cast<const uint4*>(p.scales + ((int64_t)gi * p.N + (int64_t)ncol * 8)));
+        z = (uint32_t)__ldg(p.qzeros + (int64_t)gi * (p.N / 8) + ncol);
+      }
+      s2[0] = sraw.x; s2[1] = sraw.y; s2[2] = sraw.z; s2[3] = sraw.w;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) zp[q] = ((z >> (4 * q)) & 0x000F000Fu) | magic;
+    }
+    mbar_wait(&full[s], ph);
+    uint8_t* st = smem + s * stage_bytes;
+    const uint32_t* raw = reinterpret_cast<const uint32_t*>(st + SK_BN * SK_BK + x_bytes);
+    uint32_t tmp[8], w[8];
+    // the two half-warps read rows 512 B apart: opposite row parity keeps them on different banks
+#pragma unroll
+    for (int r = 0; r < 8; ++r) tmp[r] = raw[(ko * 8 + (r ^ h)) * 16 + c];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      w[2 * q] = h ? tmp[2 * q + 1] : tmp[2 * q];
+      w[2 * q + 1] = h ? tmp[2 * q] : tmp[2 * q + 1];
+    }
+    uint8_t* arow = st + c * 128 + ((ko ^ (c & 7)) << 4);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {  // columns 2q (low halves) and 2q + 1 (high halves) of the packed word's 8
+      uint32_t v[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const uint32_t t = ((w[r] >> (4 * q)) & 0x000F000Fu) | magic;
+        if constexpr (BF) {
+          const __nv_bfloat162 d = __hsub2(*reinterpret_cast<const __nv_bfloat162*>(&t), *reinterpret_cast<const __nv_bfloat162*>(&zp[q]));
+          const __nv_bfloat162 m = __hmul2(d, *reinterpret_cast<const __nv_bfloat162*>(&s2[q]));
+          v[r] = *reinterpret_cast<const uint32_t*>(&m);
+        } else {
+          const __half2 d = __hsub2(*reinterpret_cast<const __half2*>(&t), *reinterpret_cast<const __half2*>(&zp[q]));
+          const __half2 m = __hmul2(d, *reinterpret_cast<const __half2*>(&s2[q]));
+          v[r] = *reinterpret_cast<const uint32_t*>(&m);
+        }
+      }
+      const uint4 lo = make_uint4(__byte_perm(v[0], v[1], 0x5410), __byte_perm(v[2], v[3], 0x5410),
+                                  __byte_perm(v[4], v[5], 0x5410), __byte_perm(v[6], v[7], 0x5410));
+      const uint4 hi = make_uint4(__byte_perm(v[0], v[1], 0x7632), __byte_perm(v[2], v[3], 0x7632),
+                                  __byte_perm(v[4], v[5], 0x7632), __byte_perm(v[6], v[7], 0x7632));
+      *reinterpret_cast<uint4*>(arow + (16 * (2 * q)) * 128) = lo;
+      *reinterpret_cast<uint4*>(arow + (16 * (2 * q + 1)) * 128) = hi;
+    }
+    fence_proxy_async();  // generic-proxy stores -> read by the tensor core through the async proxy
+    mbar_arrive(&afull[s]);
+  }
+}
+
 template <int MODE, int COLS, int GROUPS>
 // (M <= 64: small enough in registers and shared memory for two CTAs per SM -- the prologue and write-out of one
 // overlap the streaming of the other, also across consecutive launches)
@@ -84,14 +162,16 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
   constexpr int NBUF = MODE == 0 ? (BUFCOLS <= 128 ? 4 : 2) : 1;
   constexpr uint32_t kTmemCols = NBUF * BUFCOLS < 32 ? 32 : NBUF * BUFCOLS;
   constexpr int NE = GROUPS * 128;  // epilogue threads
+  constexpr int RAW_BYTES = MODE == 2 ? 64 * 64 : 0;  // AWQ: 64 k-rows x 16 packed words
   const int x_bytes = p.mt_pad * SK_BK;
-  const int stage_bytes = SK_BN * SK_BK + x_bytes;
+  const int stage_bytes = SK_BN * SK_BK + x_bytes + RAW_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
   uint64_t* empty = full + SK_MAX_STAGES;
   uint64_t* tfull = empty + SK_MAX_STAGES;
   uint64_t* tempty = tfull + 4;
   uint64_t* xbar = tempty + 4;  // split-K exchange: incoming partial slices (one phase per pass)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xbar + 1);
+  uint64_t* afull = xbar + 1;  // MODE 2: the dequantised operand tile of the stage is complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(afull + SK_MAX_STAGES);
   float* tab = reinterpret_cast<float*>(smem + p.stages * stage_bytes + 512);  // MODE 0: [tab_cap][mt_pad]; MODE 1: sa[256]
   // after the k-loop the (drained) stage ring is reused: send[P][128] fp32 then recv[S-1][slice][128]
   float* send = reinterpret_cast<float*>(smem);
@@ -115,6 +195,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
+      mbar_init(&afull[s], 128);
     }
     for (int a = 0; a < NBUF; ++a) {
       mbar_init(&tfull[a], 1);
@@ -138,9 +219,11 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
     const uint64_t pol_w = make_policy_evict_first();
     // weights do not depend on the previous kernel: fill the ring with them before waiting for it
     const int pre = nkb < p.stages ? nkb : p.stages;
+    const uint32_t tx_bytes = MODE == 2 ? RAW_BYTES + x_bytes : ((p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
     for (int i = pidx; i < pre; i += SK_NPROD) {
-      mbar_arrive_expect_tx(&full[i], (p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
-      tma_load_2d_hint(smem + i * stage_bytes, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[i], pol_w);
+      mbar_arrive_expect_tx(&full[i], tx_bytes);
+      if (MODE == 2) tma_load_2d_hint(smem + i * stage_bytes + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[i], pol_w);
+      else tma_load_2d_hint(smem + i * stage_bytes, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[i], pol_w);
     }
     griddep_wait();
     for (int i = pidx; i < pre; i += SK_NPROD)
@@ -151,21 +234,25 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
       const int s = i % p.stages;
       const uint32_t ph = (i / p.stages) & 1;
       mbar_wait(&empty[s], ph ^ 1);
-      mbar_arrive_expect_tx(&full[s], (p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
+      mbar_arrive_expect_tx(&full[s], tx_bytes);
       uint8_t* st = smem + s * stage_bytes;
-      tma_load_2d_hint(st, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[s], pol_w);
+      if (MODE == 2) tma_load_2d_hint(st + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[s], pol_w);
+      else tma_load_2d_hint(st, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[s], pol_w);
       if (!(p.debug & 8)) tma_load_2d(st + SK_BN * SK_BK, &tma_x, SK_KB(i) * SK_BK, 0, &full[s]);
     }
   } else if (warp == 1 && lane == 0) {
     // ================================ MMA issuer ================================
-    const uint32_t idesc = MODE == 0 ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, SK_BN, p.mt_pad)
-                                     : umma_idesc(2 /*s32*/, 1 /*s8*/, 1, SK_BN, p.mt_pad);
+    const uint32_t hfmt = p.out_bf16 ? 1u : 0u;  // kind::f16 operand format: 0 = f16, 1 = bf16
+    const uint32_t idesc = MODE == 0   ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, SK_BN, p.mt_pad)
+                           : MODE == 1 ? umma_idesc(2 /*s32*/, 1 /*s8*/, 1, SK_BN, p.mt_pad)
+                                       : umma_idesc(1 /*f32*/, hfmt, hfmt, SK_BN, p.mt_pad);
     for (int i = 0; i < nkb; ++i) {
       const int s = i % p.stages;
       const uint32_t ph = (i / p.stages) & 1;
       const int a = MODE == 0 ? (i % NBUF) : 0;
       if (MODE == 0) mbar_wait(&tempty[a], ((i / NBUF) & 1) ^ 1);
       mbar_wait(&full[s], ph);
+      if (MODE == 2) mbar_wait(&afull[s], ph);
       tc_fence_after();
       const uint32_t w_addr = smem_u32(smem + s * stage_bytes);
       const uint64_t adesc = umma_desc_k_sw128(w_addr);
@@ -175,7 +262,8 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
       for (int k = 0; k < SK_BK / 32; ++k) {
         const uint32_t accum = MODE == 0 ? (k > 0) : (i > 0 || k > 0);
         if (MODE == 0) umma_f8f6f4(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
-        else umma_i8(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+        else if (MODE == 1) umma_i8(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+        else umma_f16(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
       }
       tc_commit(&empty[s]);
       if (MODE == 0 || i == nkb - 1) tc_commit(&tfull[a]);
@@ -255,7 +343,12 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
         }
       }
     } else {
-      for (int m = et_all; m < 256; m += NE) tab[m] = m < p.M ? __ldg(p.sa + m) : 0.f;  // per-token scales
+      if (MODE == 1) {
+        for (int m = et_all; m < 256; m += NE) tab[m] = m < p.M ? __ldg(p.sa + m) : 0.f;  // per-token scales
+      } else {
+        if (p.out_bf16) awq_dequant_stages<true, GROUPS>(p, smem, full, afull, stage_bytes, x_bytes, tile, kb0, nkb, rot, grp, row);
+        else awq_dequant_stages<false, GROUPS>(p, smem, full, afull, stage_bytes, x_bytes, tile, kb0, nkb, rot, grp, row);
+      }
       mbar_wait(&tfull[0], 0);
       tc_fence_after();
 #pragma unroll
@@ -265,7 +358,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
           tmem_ld_32x32(lane_addr + c * 32, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) acc[c * 32 + j] = __uint_as_float(r[j]);  // raw int32 bits
+          for (int j = 0; j < 32; ++j) acc[c * 32 + j] = __uint_as_float(r[j]);  // raw int32 bits (MODE 1) / fp32 (MODE 2)
         }
       }
       tc_fence_before();
@@ -279,6 +372,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
   const int passes = (p.mt_pad + P - 1) / P;
   const int slice = (P + S - 1) / S;
   float* recv = send + P * SK_BN;  // [S-1][slice][128]: slot (src - me - 1) mod S holds the partial of CTA src
+  const int srow = MODE == 2 ? 8 * (row & 15) + (row >> 4) : row;  // tile column held by this TMEM lane
   for (int ps = 0; ps < passes; ++ps) {
     const int t0 = ps * P;
     const int pt = p.mt_pad - t0 < P ? p.mt_pad - t0 : P;
@@ -289,7 +383,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
     if (warp >= SK_NONEPI && col0 >= t0 && col0 < t0 + pt) {
 #pragma unroll
       for (int j = 0; j < COLS; ++j)
-        if (j < ncols) send[(col0 - t0 + j) * SK_BN + row] = acc[j];
+        if (j < ncols) send[(col0 - t0 + j) * SK_BN + srow] = acc[j];
       if (S > 1) fence_proxy_async();  // the bulk copies below read these through the async proxy
     }
     if (S > 1) {
@@ -323,9 +417,11 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
       const int n_in = 2 * pi, n = tile * SK_BN + n_in;
       const bool pair_ok = (n + 1 < p.N) && (p.ldo % 2 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 3) == 0);
       float sb0 = 1.f, sb1 = 1.f, b0 = 0.f, b1 = 0.f;
-      if (MODE == 1) {
-        sb0 = n < p.N ? __ldg(p.sb + n) : 0.f;
-        sb1 = n + 1 < p.N ? __ldg(p.sb + n + 1) : 0.f;
+      if (MODE != 0) {
+        if (MODE == 1) {
+          sb0 = n < p.N ? __ldg(p.sb + n) : 0.f;
+          sb1 = n + 1 < p.N ? __ldg(p.sb + n + 1) : 0.f;
+        }
         if (p.bias) {
           const uint16_t* bp = reinterpret_cast<const uint16_t*>(p.bias);
           const uint16_t u0 = n < p.N ? __ldg(bp + n) : (uint16_t)0, u1 = n + 1 < p.N ? __ldg(bp + n + 1) : (uint16_t)0;
@@ -346,7 +442,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
           }
         }
         float o0, o1;
-        if (MODE == 0) {
+        if (MODE != 1) {
           o0 = v[0].x;
           o1 = v[0].y;
 #pragma unroll
@@ -355,6 +451,10 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
               o0 += v[s2].x;
               o1 += v[s2].y;
             }
+          if (MODE == 2 && p.bias) {
+            o0 += b0;
+            o1 += b1;
+          }
         } else {
           int i0 = __float_as_int(v[0].x), i1 = __float_as_int(v[0].y);
 #pragma unroll
@@ -419,7 +519,7 @@ static SkinnyPlan skinny_plan(int mode, int mt_pad) {
   // (kernels that allocate tensor memory are scheduled one CTA per SM: cudaOccupancyMaxActiveBlocksPerMultiprocessor
   // answers 1 whatever the shared-memory and register footprint, measured)
   const int budget = mt_pad <= 64 ? 112 * 1024 : 226 * 1024;
-  const int stage_bytes = SK_BN * SK_BK + mt_pad * SK_BK;
+  const int stage_bytes = SK_BN * SK_BK + mt_pad * SK_BK + (mode == 2 ? 4096 : 0);
   const int tab_bytes = mode == 0 ? (mt_pad <= 64 ? 8192 : mt_pad <= 128 ? 16384 : 32768) : 1024;
   pl.tab_cap = mode == 0 ? tab_bytes / (mt_pad * 4) : 0;
   int stages = (budget - SK_FIXED_SMEM - tab_bytes) / stage_bytes;
@@ -471,7 +571,7 @@ static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, SkinnyP
   }
   // K slices per n-tile = cluster size: the S that puts the most CTAs to work while every CTA of (tiles x S) is
   // resident at once, owns at least two k-blocks, and the exchange buffers fit in the drained ring
-  const int ring_bytes = sp.stages * (SK_BN * SK_BK + sp.mt_pad * SK_BK);
+  const int ring_bytes = sp.stages * (SK_BN * SK_BK + sp.mt_pad * SK_BK + (MODE == 2 ? 4096 : 0));
   const int P = sp.mt_pad < 128 ? sp.mt_pad : 128;
   int S = 1, best = sp.n_tiles < capacity[1] ? sp.n_tiles : capacity[1];
   for (int s2 = 2; s2 <= SK_MAX_SPLITS; ++s2) {
@@ -531,7 +631,7 @@ int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, Skinny
   sp.stamps = nullptr;
   sp.mt_pad = skinny_mt_pad(sp.M);
   sp.n_tiles = (sp.N + SK_BN - 1) / SK_BN;
-  sp.kb_total = (sp.K + SK_BK - 1) / SK_BK;
+  sp.kb_total = ((MODE == 2 ? 2 * sp.K : sp.K) + SK_BK - 1) / SK_BK;  // 128 operand bytes per k-block
   const SkinnyPlan pl = skinny_plan(MODE, sp.mt_pad);
   sp.stages = pl.stages;
   sp.tab_cap = pl.tab_cap;
@@ -541,11 +641,18 @@ int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, Skinny
     sp.debug = dbg;
     if ((dbg & 256) && workspace && workspace_bytes >= (size_t)sp.n_tiles * 8 * 64) sp.stamps = (unsigned long long*)workspace;
   }
-  B200_REQUIRE(pl.stages >= 2 && (sp.mt_pad < 128 ? sp.mt_pad : 128) * 512 <= pl.stages * (SK_BN * SK_BK + sp.mt_pad * SK_BK), B200_ERR_UNSUPPORTED,
+  B200_REQUIRE(pl.stages >= 2 && (sp.mt_pad < 128 ? sp.mt_pad : 128) * 512 <= pl.stages * (SK_BN * SK_BK + sp.mt_pad * SK_BK + (MODE == 2 ? 4096 : 0)), B200_ERR_UNSUPPORTED,
                "gemm_skinny: shared-memory plan does not fit (M=%d)", sp.M);
   CUtensorMap tw, tx;
-  if (int rc = make_tmap_2d(&tw, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.N, sp.K, ldw, SK_BN, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
-  if (int rc = make_tmap_2d(&tx, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.M, sp.K, lda, sp.mt_pad, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+  if (MODE == 2) {
+    // w = qweight int32 [K, N/8] (row pitch ldw bytes): box of 64 k-rows x 64 bytes (16 words = 128 columns), dense;
+    // a = half activations [M, K], addressed in bytes like the 1-byte modes (128 bytes = 64 k per block)
+    if (int rc = make_tmap_2d(&tw, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.K, (uint64_t)sp.N / 2, ldw, 64, 64, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+    if (int rc = make_tmap_2d(&tx, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.M, (uint64_t)sp.K * 2, lda, sp.mt_pad, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+  } else {
+    if (int rc = make_tmap_2d(&tw, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.N, sp.K, ldw, SK_BN, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+    if (int rc = make_tmap_2d(&tx, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.M, sp.K, lda, sp.mt_pad, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+  }
   if (sp.mt_pad <= 64) return launch_skinny_t<MODE, 32, 2>(tw, tx, sp, pl.smem, st);
   if (sp.mt_pad <= 128) return launch_skinny_t<MODE, 32, 4>(tw, tx, sp, pl.smem, st);
   return launch_skinny_t<MODE, 64, 4>(tw, tx, sp, pl.smem, st);
@@ -553,5 +660,6 @@ int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, Skinny
 
 template int launch_skinny<0>(const void*, int64_t, const void*, int64_t, SkinnyParams&, void*, size_t, cudaStream_t);
 template int launch_skinny<1>(const void*, int64_t, const void*, int64_t, SkinnyParams&, void*, size_t, cudaStream_t);
+template int launch_skinny<2>(const void*, int64_t, const void*, int64_t, SkinnyParams&, void*, size_t, cudaStream_t);
 
 }  // namespace b200

@@ -10,6 +10,10 @@ struct SkinnyParams {
   const float* sb;
   int64_t sb_sk, sb_sn;
   const void* bias;
+  // MODE 2 (AWQ W4A16): zero points int32 [K/group, N/8], scales half [K/group, N], group size (multiple of 8)
+  const int32_t* qzeros;
+  const uint16_t* scales;
+  int group;
   void* out;
   int64_t ldo;
   int out_bf16;
@@ -24,7 +28,8 @@ struct SkinnyParams {
 
 size_t skinny_workspace_bytes(int M, int N, int K);
 bool skinny_applicable(int M);
-// a [M,K] activations, w [N,K] weight (both K-major, 1-byte elements); MODE 0 fp8 block-scaled, 1 int8
+// a [M,K] activations, w [N,K] weight (both K-major, 1-byte elements); MODE 0 fp8 block-scaled, 1 int8;
+// MODE 2: a = half activations [M,K] (lda in BYTES), w = AWQ qweight int32 [K, N/8] (ldw in BYTES)
 template <int MODE>
 int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, SkinnyParams& sp, void* workspace,
                   size_t workspace_bytes, cudaStream_t st);

@@ -48,7 +48,8 @@ def test_size_queries_need_no_gpu():
     assert lib.b200_decode_attn_num_splits(64, 32, 8, 128, 128, 4096, 5) == 1
     assert lib.b200_decode_attn_num_splits(64, 32, 8, 96, 96, 4096, 5) == 5
     assert lib.b200_gemm_workspace_size(64, 4096, 4096) > 16
-    assert lib.b200_awq_w4a16_workspace_size(16, 1024, 512) >= 1024 * 512 * 2
+    assert lib.b200_awq_w4a16_workspace_size(16, 1024, 512) >= 256  # fused decode path: no weight staging
+    assert lib.b200_awq_w4a16_workspace_size(1024, 1024, 512) >= 1024 * 512 * 2  # two-phase path (M > 256)
 
 
 def test_cpu_tensors_are_rejected():

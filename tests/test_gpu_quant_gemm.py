@@ -192,3 +192,42 @@ def test_awq_w4a16_gemm(M, K, N, dt):
     out = ops.awq_w4a16_gemm(x.cuda(), qw.cuda(), sc.cuda(), qz.cuda(), bias.cuda() if bias is not None else None)
     assert rel_l2(out, ref) < 1e-2
     assert rel_l2(out, ref) < 2e-3
+
+
+@pytest.mark.parametrize("K,N,group,dt", [(128, 256, 128, torch.float16), (256, 1088, 128, torch.bfloat16),
+                                          (256, 512, 32, torch.float16), (192, 160, 64, torch.bfloat16)])
+def test_awq_fused_gemm_dequant_is_bit_exact(K, N, group, dt):
+    """Identity activations read the dequantised weight back through the fused kernel (int4 box -> registers ->
+    swizzled tcgen05 operand tile -> TMEM -> permuted write-out): it must equal awq_dequantize bit for bit."""
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(K + N + group)
+    qw = torch.randint(-2 ** 31, 2 ** 31 - 1, (K, N // 8), generator=g, dtype=torch.int32)
+    qz = torch.randint(-2 ** 31, 2 ** 31 - 1, (K // group, N // 8), generator=g, dtype=torch.int32)
+    sc = (torch.rand(K // group, N, generator=g) * 0.02 + 1e-3).to(dt)
+    ref = orc.awq_dequantize(qw, sc, qz)
+    out = ops.awq_w4a16_gemm(torch.eye(K, dtype=dt).cuda(), qw.cuda(), sc.cuda(), qz.cuda())
+    assert torch.equal(out.cpu().view(torch.int16), ref.view(torch.int16))
+
+
+@pytest.mark.parametrize("M", [1, 7, 64, 128, 200, 256])
+@pytest.mark.parametrize("N,K", [(3584, 5120), (5120, 2560), (27648, 5120), (5120, 13824)])  # cfg 3 under TP2 (SURVEY 8a a15)
+def test_awq_fused_gemm_cfg3_shapes(M, N, K):
+    from iaas_sglang_b200 import ops
+
+    dt = torch.bfloat16
+    g = torch.Generator().manual_seed(M + K + N)
+    qw = torch.randint(-2 ** 31, 2 ** 31 - 1, (K, N // 8), generator=g, dtype=torch.int32)
+    qz = torch.randint(-2 ** 31, 2 ** 31 - 1, (K // 128, N // 8), generator=g, dtype=torch.int32)
+    sc = (torch.rand(K // 128, N, generator=g) * 0.01 + 1e-3).to(dt)
+    x = torch.randn(M, K, generator=g).to(dt)
+    bias = torch.randn(N, generator=g).to(dt) if M % 2 == 0 else None
+    # awq.py:186-204 literally: dequantise (oracle, bit-exact to awq_dequantize), then matmul (fp32 accumulation)
+    ref = x.float() @ orc.awq_dequantize(qw, sc, qz).float()
+    if bias is not None:
+        ref += bias.float()
+    out = ops.awq_w4a16_gemm(x.cuda(), qw.cuda(), sc.cuda(), qz.cuda(), bias.cuda() if bias is not None else None)
+    assert rel_l2(out.cpu().float(), ref) < 2e-3
+    # the same call again gives the same bits (fixed-order split-K reduction)
+    out2 = ops.awq_w4a16_gemm(x.cuda(), qw.cuda(), sc.cuda(), qz.cuda(), bias.cuda() if bias is not None else None)
+    assert torch.equal(out, out2)

@@ -585,8 +585,20 @@ def main():
                 line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        # NCCL teardown with captured collectives still alive can block for minutes (seen on the 2-GPU box: the JSON
+        # line was out, destroy_process_group never returned).  The measurement is complete: leave through a last
+        # barrier with a watchdog, and skip the communicator teardown.
+        sys.stdout.flush()
+        watchdog = threading.Timer(20.0, lambda: os._exit(0))
+        watchdog.daemon = True
+        watchdog.start()
+        try:
+            torch.cuda.synchronize()
+            dist.barrier()
+        finally:
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
 
 
 if __name__ == "__main__":

@@ -7,6 +7,8 @@
 // buffer in the caller's workspace (so both GEMM operands are K-major / SWIZZLE_128B TMA tiles),
 // then gemm_tc_kernel<MODE 2> (tcgen05.mma kind::f16, fp32 accumulate in TMEM) does x . W^T.
 // The dequantised values are bit-identical to awq_dequantize (awq_kernel.cu:126-221).
+#include <stdlib.h>
+
 #include "gemm_skinny.h"
 
 namespace b200 {
@@ -14,6 +16,10 @@ namespace b200 {
 int dense_half_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, const void* bias, void* out, int64_t ldo,
                     int dtype, int M, int N, int K, void* workspace, size_t workspace_bytes, cudaStream_t st);
 size_t dense_half_gemm_workspace(int M, int N, int K);
+// awq_fused.cu: NT sub-tiles per CTA, separate operand ring (N % 128 == 0)
+bool awq_fused_applicable(int M, int N, int K, int group);
+int launch_awq_fused(const void* x, int64_t ldx, const int32_t* qweight, const void* scales, const int32_t* qzeros,
+                     const void* bias, void* out, int64_t ldo, int dtype, int M, int N, int K, int group, cudaStream_t st);
 
 // block = (32, 8): tile of 64 K-rows x 32 packed columns (= 256 N); out_t[n, k]
 template <bool BF16>
@@ -73,6 +79,10 @@ extern "C" int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qwei
   cudaStream_t st = (cudaStream_t)stream;
   if (awq_fused_shape(M, N, K) && group % 8 == 0 && ldx % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)qweight & 15) == 0 &&
       ((uintptr_t)scales & 15) == 0) {
+    static int use_v2 = -1;
+    if (use_v2 < 0) { const char* e = getenv("B200_AWQ_V1"); use_v2 = (e && atoi(e)) ? 0 : 1; }
+    if (use_v2 && awq_fused_applicable(M, N, K, group))
+      return launch_awq_fused(x, ldx, qweight, scales, qzeros, bias, out, ldo, dtype, M, N, K, group, st);
     SkinnyParams sp{};
     sp.bias = bias; sp.out = out; sp.ldo = ldo; sp.out_bf16 = dtype == B200_BF16;
     sp.qzeros = qzeros; sp.scales = (const uint16_t*)scales; sp.group = group;

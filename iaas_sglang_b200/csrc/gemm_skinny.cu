@@ -109,6 +109,10 @@ __device__ __forceinline__ void awq_dequant_stages(const SkinnyParams& p, uint8_
       for (int q = 0; q < 4; ++q) zp[q] = ((z >> (4 * q)) & 0x000F000Fu) | magic;
     }
     mbar_wait(&full[s], ph);
+    if (p.debug & 32) {  // developer probe: no dequantisation (wrong results), what is left is the pipeline
+      mbar_arrive(&afull[s]);
+      continue;
+    }
     uint8_t* st = smem + s * stage_bytes;
     const uint32_t* raw = reinterpret_cast<const uint32_t*>(st + SK_BN * SK_BK + x_bytes);
     uint32_t tmp[8], w[8];
@@ -219,7 +223,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
     const uint64_t pol_w = make_policy_evict_first();
     // weights do not depend on the previous kernel: fill the ring with them before waiting for it
     const int pre = nkb < p.stages ? nkb : p.stages;
-    const uint32_t tx_bytes = MODE == 2 ? RAW_BYTES + x_bytes : ((p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
+    const uint32_t tx_bytes = MODE == 2 ? RAW_BYTES + ((p.debug & 8) ? 0 : x_bytes) : ((p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
     for (int i = pidx; i < pre; i += SK_NPROD) {
       mbar_arrive_expect_tx(&full[i], tx_bytes);
       if (MODE == 2) tma_load_2d_hint(smem + i * stage_bytes + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[i], pol_w);

@@ -125,6 +125,11 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
   constexpr uint32_t kTmemCols = NT * BUFCOLS <= 32 ? 32 : NT * BUFCOLS <= 64 ? 64 : NT * BUFCOLS <= 128 ? 128 : NT * BUFCOLS <= 256 ? 256 : 512;
   static_assert(NT * BUFCOLS <= 512, "tensor memory");
   constexpr int NE = GROUPS * 128;
+  constexpr int TEAM = NT * 128 < NE ? NT * 128 : NE;    // dequantiser threads per stage
+  constexpr int NTEAMS = NE / TEAM;                      // teams take alternate stages
+  constexpr int ITEMS = (NT * 128 + TEAM - 1) / TEAM;    // items per thread per stage
+  constexpr int RB = NTEAMS > AQ_NA ? NTEAMS : AQ_NA;    // "operand buffer free" barriers (see gfree)
+  static_assert(RB <= 4 && RB % NTEAMS == 0 && RB % AQ_NA == 0, "free-barrier rotation");
   constexpr int A_RING = AQ_NA * NT * AQ_BN * AQ_BK;
   const int x_bytes = p.mt_pad * AQ_BK;
   const int stage_bytes = x_bytes + NT * AQ_RAW;  // [activation tile][NT raw boxes]
@@ -132,9 +137,9 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
   uint64_t* full = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
   uint64_t* empty = full + AQ_MAX_STAGES;
   uint64_t* afull = empty + AQ_MAX_STAGES;
-  // "operand buffer free" is signalled per dequantiser GROUP (the group that will refill the buffer), not per buffer:
-  // with more groups than buffers a per-buffer barrier could run two phases ahead of a waiting group, which a parity
-  // wait cannot tell from zero phases (seen as a hang at M = 128)
+  // "operand buffer free": the MMA thread signals barrier (j + NA) % RB after stage j, stage i waits on barrier i % RB
+  // (RB = max(teams, buffers)).  A per-buffer barrier alone could run two phases ahead of a waiting team when there are
+  // more teams than buffers, which a parity wait cannot tell from zero phases (seen as a hang at M = 128).
   uint64_t* gfree = afull + AQ_NA;
   uint64_t* tfull = gfree + 4;
   uint64_t* xbar = tfull + 1;
@@ -157,8 +162,8 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    for (int a = 0; a < AQ_NA; ++a) mbar_init(&afull[a], 128);
-    for (int g = 0; g < GROUPS; ++g) mbar_init(&gfree[g], 1);
+    for (int a = 0; a < AQ_NA; ++a) mbar_init(&afull[a], TEAM);
+    for (int g = 0; g < RB; ++g) mbar_init(&gfree[g], 1);
     mbar_init(tfull, 1);
     mbar_init(xbar, 1);
     fence_mbar_init();
@@ -211,7 +216,7 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
         for (int k = 0; k < AQ_BK / 32; ++k) umma_f16(tmem_base + u * BUFCOLS, adesc + 2 * k, bdesc + 2 * k, idesc, (i > 0 || k > 0));
       }
       tc_commit(&empty[s]);
-      tc_commit(&gfree[(i + AQ_NA) % GROUPS]);  // stage i + NA reuses this operand buffer
+      tc_commit(&gfree[(i + AQ_NA) % RB]);  // stage i + NA reuses this operand buffer
       if (i == nkb - 1) tc_commit(tfull);
     }
   }
@@ -225,41 +230,50 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
   const int nchunk = (ncols + 31) / 32;
 
   if (warp >= AQ_NONEPI) {
-    // ================================ dequantiser groups: stage i belongs to group i % GROUPS ================================
+    // ================================ dequantiser teams ================================
+    // A stage holds NT x 128 items (one per (sub-tile, packed word column, k-octet)).  TEAM = min(NE, NT x 128) threads
+    // work on ONE stage together, so a stage is dequantised in about one item's latency and the two operand buffers
+    // are enough to keep the tensor core fed; the NE / TEAM teams take alternate stages.
     griddep_wait();
-    const int c = row & 15, ko = row >> 4, h = ko & 1;
+    const int team = et_all / TEAM, tt = et_all - team * TEAM;
     constexpr uint32_t magic = BF ? 0x43004300u : 0x64006400u;
+    const int c = tt & 15, ko = (tt >> 4) & 7, h = ko & 1;  // (TEAM and 128 are multiples of 128: same for all items)
     int cur_g = -1;
-    uint32_t zp[NT][4], s2[NT][4];
-    static_assert(GROUPS >= AQ_NA, "a group must not own two operand buffers in flight");
-    for (int i = grp, kq = 0; i < nkb; i += GROUPS, ++kq) {
-      const int s = i % p.stages, a = i % AQ_NA;
-      const int gi = ((kb0 + i) * 64 + ko * 8) / p.group;  // this thread's 8 k-rows share a group (group % 8 == 0)
-      if (gi != cur_g) {
-        cur_g = gi;
+    uint32_t zp[ITEMS][4], s2[ITEMS][4];
+    if (team < NTEAMS) {
+      for (int i = team; i < nkb; i += NTEAMS) {
+        const int s = i % p.stages, a = i % AQ_NA;
+        const int gi = ((kb0 + i) * 64 + ko * 8) / p.group;  // this thread's 8 k-rows share a group (group % 8 == 0)
+        if (gi != cur_g) {
+          cur_g = gi;
 #pragma unroll
-        for (int u = 0; u < NT; ++u) {
-          const int ncol = (tile * NT + u) * 16 + c;
-          uint4 sraw = make_uint4(0u, 0u, 0u, 0u);
-          uint32_t z = 0;
-          if (ncol * 8 < p.N) {
-            sraw = __ldg(reinterpret_cast<const uint4*>(p.scales + ((int64_t)gi * p.N + (int64_t)ncol * 8)));
-            z = (uint32_t)__ldg(p.qzeros + (int64_t)gi * (p.N / 8) + ncol);
+          for (int it = 0; it < ITEMS; ++it) {
+            const int u = (tt + it * TEAM) >> 7;
+            const int ncol = (tile * NT + u) * 16 + c;
+            uint4 sraw = make_uint4(0u, 0u, 0u, 0u);
+            uint32_t z = 0;
+            if (u < NT && ncol * 8 < p.N) {
+              sraw = __ldg(reinterpret_cast<const uint4*>(p.scales + ((int64_t)gi * p.N + (int64_t)ncol * 8)));
+              z = (uint32_t)__ldg(p.qzeros + (int64_t)gi * (p.N / 8) + ncol);
+            }
+            s2[it][0] = sraw.x; s2[it][1] = sraw.y; s2[it][2] = sraw.z; s2[it][3] = sraw.w;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) zp[it][q] = ((z >> (4 * q)) & 0x000F000Fu) | magic;
           }
-          s2[u][0] = sraw.x; s2[u][1] = sraw.y; s2[u][2] = sraw.z; s2[u][3] = sraw.w;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) zp[u][q] = ((z >> (4 * q)) & 0x000F000Fu) | magic;
         }
-      }
-      // the MMAs of stage i - NA, which read this operand buffer, have completed (this group's kq-th such signal)
-      if (i >= AQ_NA) mbar_wait(&gfree[grp], (uint32_t)((grp < AQ_NA ? kq - 1 : kq) & 1));
-      mbar_wait(&full[s], (i / p.stages) & 1);
-      const uint8_t* st = ring + s * stage_bytes + x_bytes;
+        // the MMAs of stage i - NA, which read this operand buffer, have completed: barrier i % R, its n-th completion
+        if (i >= AQ_NA) mbar_wait(&gfree[i % RB], (uint32_t)((i / RB - ((i % RB) < AQ_NA ? 1 : 0)) & 1));
+        mbar_wait(&full[s], (i / p.stages) & 1);
+        const uint8_t* st = ring + s * stage_bytes + x_bytes;
 #pragma unroll
-      for (int u = 0; u < NT; ++u)
-        aq_dequant_item<BF>(reinterpret_cast<const uint32_t*>(st + u * AQ_RAW), smem + (a * NT + u) * (AQ_BN * AQ_BK), c, ko, h, zp[u], s2[u]);
-      fence_proxy_async();  // generic-proxy stores -> read by the tensor core through the async proxy
-      mbar_arrive(&afull[a]);
+        for (int it = 0; it < ITEMS; ++it) {
+          const int u = (tt + it * TEAM) >> 7;
+          if (u < NT)
+            aq_dequant_item<BF>(reinterpret_cast<const uint32_t*>(st + u * AQ_RAW), smem + (a * NT + u) * (AQ_BN * AQ_BK), c, ko, h, zp[it], s2[it]);
+        }
+        fence_proxy_async();  // generic-proxy stores -> read by the tensor core through the async proxy
+        mbar_arrive(&afull[a]);
+      }
     }
     mbar_wait(tfull, 0);
     tc_fence_after();
@@ -271,7 +285,10 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
   const int passes = (p.mt_pad + P - 1) / P;
   const int slice = (P + S - 1) / S;
   float* recv = send + P * AQ_BN;  // [S-1][slice][128]: slot (src - me - 1) mod S holds the partial of CTA src
-  const int srow = 8 * (row & 15) + (row >> 4);  // sub-tile column held by this TMEM lane
+  // sub-tile column n held by this TMEM lane, stored at physical column n ^ (((n >> 5) & 3) << 1): without the XOR a
+  // warp's 32 columns {8a + b} fall on four banks (eight-way conflict on every one of the COLS stores per thread)
+  const int scol = 8 * (row & 15) + (row >> 4);
+  const int srow = scol ^ (((scol >> 5) & 3) << 1);
   uint32_t xph = 0;
   for (int u = 0; u < NT; ++u) {
     const int tile_n = tile * NT + u;
@@ -343,7 +360,7 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
           for (int s2i = 0; s2i < AQ_MAX_SPLITS; ++s2i) {
             if (s2i < S) {
               const float* src = s2i == rank ? send + (my0 + tk) * AQ_BN : recv + (((s2i - rank - 1 + S) % S) * slice + tk) * AQ_BN;
-              const float2 v = *reinterpret_cast<const float2*>(src + n_in);
+              const float2 v = *reinterpret_cast<const float2*>(src + (n_in ^ (((n_in >> 5) & 3) << 1)));
               o0 = s2i == 0 ? v.x : o0 + v.x;
               o1 = s2i == 0 ? v.y : o1 + v.y;
             }
@@ -393,6 +410,39 @@ static int aq_stages(int mt_pad, int nt) {
   return st > AQ_MAX_STAGES ? AQ_MAX_STAGES : st;
 }
 
+// CTAs that can be resident at once when launched as clusters of S (one CTA per SM; a cluster lives inside one GPC, so
+// S = 5 or 7 strands SMs: asking for 28 x 5 CTAs ran as two waves before this was queried)
+static int aq_cluster_capacity(int S) {
+  static int cap[AQ_MAX_SPLITS + 1] = {0};
+  static bool done = false;
+  if (!done) {
+    auto kern = awq_fused_kernel<32, 4, 1, true>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
+    for (int s = 1; s <= AQ_MAX_SPLITS; ++s) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.blockDim = dim3((AQ_NONEPI + 16) * 32);
+      cfg.gridDim = dim3(1, s);
+      cfg.dynamicSmemBytes = 215 * 1024;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 1;
+      attr[0].val.clusterDim.y = s;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      int ncl = 0;
+      if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) != cudaSuccess || ncl <= 0) {
+        cudaGetLastError();
+        ncl = (sms / 8 / s) * 8;  // eight GPCs, conservative
+      }
+      cap[s] = ncl * s;
+    }
+    done = true;
+  }
+  return cap[S];
+}
+
 // pick (NT, S): one wave of (n-tiles x S) CTAs where possible; cost in "sub-tile stages" per CTA, with the activation
 // traffic (re-staged once per CTA and stage, whatever NT) as a surcharge that shrinks with NT
 static AwqPlan aq_plan(int M, int N, int K, int mt_pad) {
@@ -413,11 +463,13 @@ static AwqPlan aq_plan(int M, int N, int K, int mt_pad) {
     const int scratch = AQ_NA * nt * AQ_BN * AQ_BK + stages * aq_stage_bytes(mt_pad, nt);
     for (int s = 1; s <= AQ_MAX_SPLITS; ++s) {
       if (force_s > 0 && s != force_s) continue;
-      if (s > 1 && (tiles * s > sms || kb / s < 2)) continue;
+      if (s > 1 && (tiles * s > aq_cluster_capacity(s) || kb / s < 2)) continue;
       const int slice = (P + s - 1) / s;
       if ((P + (s - 1) * slice) * AQ_BN * 4 > scratch) continue;
       const int waves = (tiles * s + sms - 1) / sms;
-      const double cost = (double)waves * nt * ((kb + s - 1) / s) * (1.0 + 0.6 / nt) + (s > 1 ? 8.0 : 0.0) + 4.0 * nt;
+      // measured (tools/kbench.py awq, B200_AWQ_NT sweep): ~0.3 us per sub-tile stage, ~0.1 us of activation staging per
+      // stage, and a write-out of ~2 us per sub-tile, ~6 us when it goes through the cluster exchange
+      const double cost = (double)waves * ((kb + s - 1) / s) * (0.3 * nt + 0.1) + nt * (s > 1 ? 5.0 + 0.25 * s : 2.0);
       if (cost < best_cost) {
         best_cost = cost;
         best = AwqPlan{nt, s, stages, 0};

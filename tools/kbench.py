@@ -294,6 +294,32 @@ def bench_mla():
     mla_case("cfg5tp8-small", 64, 16, 4096, layers=4, splits=8)
 
 
+def _plain_timeit():
+    """no graph, 4 launches: for runs under ncu"""
+    global timeit
+
+    def timeit(fn, n_variants, reps=0, warm=3):  # noqa: F811
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn(0); fn(1 % n_variants)
+        e0.record()
+        fn(0); fn(1 % n_variants)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 2
+
+
+def bench_profmla():
+    """a few plain launches of the cfg 5 per-GPU MLA shape for ncu (-k regex:decode_mla)"""
+    _plain_timeit()
+    mla_case("cfg5tp8", 256, 16, 16384)
+
+
+def bench_profawq():
+    """a few plain launches of the cfg 3 gate_up AWQ shape for ncu (-k regex:awq_fused)"""
+    _plain_timeit()
+    awq_case(128, 27648, 5120)
+
+
 def main():
     what = sys.argv[1:] or ["attn", "gemm", "gemm_big", "int8", "awq"]
     print(f"# peaks: HBM {HBM} GB/s, bf16 {BF16_TF} TFLOP/s (MEASURED_PEAKS.json or fallback)")

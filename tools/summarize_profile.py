@@ -18,12 +18,12 @@ import sys
 from collections import OrderedDict
 
 
-def launches(src: str, dst: str, start_re: str = r"b200::rmsnorm_kernel"):
+def launches(src: str, dst: str, start_re: str = r"rmsnorm_kernel"):
     rows = [r for r in csv.reader(open(src)) if len(r) > 10]
     hdr = rows[0]
     ki, vi, gi, bi = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size"), hdr.index("Block Size")
     data = rows[1:]
-    ours = [r for r in data if "b200::" in r[ki]]
+    ours = [r for r in data if "b200::" in r[ki] or re.match(r"(void )?(decode_|gemm_|rmsnorm|group_quant|rope_|silu_|awq_|per_token|set_kv)", r[ki])]
     # one step = from the first rmsnorm of a pass to the next pass's first rmsnorm; use the LAST complete pass
     names = [re.sub(r"\(.*", "", r[ki]).replace("void ", "") for r in ours]
     agg: "OrderedDict[str, list]" = OrderedDict()

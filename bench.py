@@ -66,6 +66,7 @@ def parse_args():
     ap.add_argument("--tp", type=int, default=0, help="emulate TP-local shapes on ONE GPU (no collectives); 0 = --gpus")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fused", action="store_true", help="separate rmsnorm / silu_and_mul / quantiser kernels (the reference's op sequence)")
     ap.add_argument("--kernels", action="store_true", help="also print per-kernel roofline lines to stderr")
     return ap.parse_args()
 
@@ -164,6 +165,7 @@ class DecodeStack:
 
         self.wl, self.L, self.B, self.tp, self.dev = wl, layers, batch, tp, dev
         self.collectives = collectives
+        self.no_fused = False
         self.dtype = torch.bfloat16
         hq, hkv, d, hidden, inter = wl["hq"], wl["hkv"], wl["d"], wl["hidden"], wl["inter"]
         assert hq % tp == 0 and inter % tp == 0 and (hkv % tp == 0 or tp % hkv == 0)
@@ -253,7 +255,7 @@ class DecodeStack:
     def _row_parallel(self, layer, x):
         from iaas_sglang_b200 import linear
 
-        return linear.row_parallel_forward(self.method, layer, x, None, reduce_results=self.collectives)
+        return linear.row_parallel_forward(self.method, layer, x, None, reduce_results=self.collectives, out_dtype=self.dtype)
 
     def forward(self) -> torch.Tensor:
         """One decode step over the static buffers (eager; also the body that gets graph-captured)."""
@@ -262,16 +264,26 @@ class DecodeStack:
         fb, d = self.fb, self.d
         h = self.hidden_in
         residual = torch.zeros_like(h)
+        fused = hasattr(self.method, "apply_quantized") and not self.no_fused
         for l in range(self.L):
-            x = ops.rmsnorm(h, self.norm1[l], 1e-5, residual=residual)       # residual += h ; x = norm(residual)
-            qkv = self.method.apply(self.w_qkv[l], x)
+            if fused:   # FP8: the norm / activation kernels emit the group-128 quantisation themselves (bit-identical)
+                xq = ops.rmsnorm_quant_fp8(h, self.norm1[l], 1e-5, residual=residual)
+                qkv = self.method.apply_quantized(self.w_qkv[l], xq[0], xq[1], self.dtype)
+            else:
+                x = ops.rmsnorm(h, self.norm1[l], 1e-5, residual=residual)       # residual += h ; x = norm(residual)
+                qkv = self.method.apply(self.w_qkv[l], x)
             q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
             ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
             a = self.attn[l](q, k, v, fb)
             h = self._row_parallel(self.w_o[l], a)
-            x = ops.rmsnorm(h, self.norm2[l], 1e-5, residual=residual)
-            gu = self.method.apply(self.w_gate_up[l], x)
-            act = ops.silu_and_mul(gu)
+            if fused:
+                xq = ops.rmsnorm_quant_fp8(h, self.norm2[l], 1e-5, residual=residual)
+                gu = self.method.apply_quantized(self.w_gate_up[l], xq[0], xq[1], self.dtype)
+                act = ops.silu_and_mul_quant_fp8(gu)
+            else:
+                x = ops.rmsnorm(h, self.norm2[l], 1e-5, residual=residual)
+                gu = self.method.apply(self.w_gate_up[l], x)
+                act = ops.silu_and_mul(gu)
             h = self._row_parallel(self.w_down[l], act)
         return ops.rmsnorm(h, self.norm_f, 1e-5, residual=residual)
 
@@ -476,6 +488,7 @@ def main():
     tp = args.tp or world
     batch = args.batch or wl["batch"] * world
     stack = DecodeStack(wl, n_layers, batch, tp, rank if world > 1 else 0, dev, collectives=world > 1)
+    stack.no_fused = args.no_fused
     torch.cuda.synchronize()
 
     def barrier():

@@ -93,6 +93,10 @@ SIGNATURES = {
     "b200_awq_w4a16_mm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                   c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p]),
+    "b200_rmsnorm_quant_fp8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64,
+                                       c_int, c_int, c_int, c_float, c_float, c_float, c_float, c_void_p]),
+    "b200_silu_mul_quant_fp8": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_int, c_int,
+                                        c_float, c_float, c_float, c_void_p]),
     "b200_silu_and_mul": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_rope_neox": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float,
                              c_void_p]),

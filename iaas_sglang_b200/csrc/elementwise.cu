@@ -207,19 +207,35 @@ __global__ void __launch_bounds__(256) silu_mul_kernel(const uint16_t* __restric
   *reinterpret_cast<uint4*>(out + m * d + c * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
 }
 
+// one CTA per token; a thread owns ONE frequency i (sin/cos evaluated once) and walks the heads with that column
 template <bool BF16>
 __global__ void rope_neox_kernel(uint16_t* __restrict__ q, int64_t q_sm, uint16_t* __restrict__ k, int64_t k_sm,
                                  const int64_t* __restrict__ pos, int Hq, int Hkv, int D, float log2_theta) {
   const int m = blockIdx.x;
   const int half = D / 2;
   const float ps = (float)pos[m];
-  const int total = (Hq + Hkv) * half;
-  for (int e = threadIdx.x; e < total; e += blockDim.x) {
-    const int h = e / half, i = e % half;
+  const int slots = blockDim.x / half;  // heads processed per pass (blockDim.x is a multiple of half, see the launcher)
+  if (slots == 0) {  // D / 2 > blockDim.x: element-wise walk
+    const int total = (Hq + Hkv) * half;
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
+      const int h = e / half, i = e % half;
+      uint16_t* base = h < Hq ? q + (int64_t)m * q_sm + h * D : k + (int64_t)m * k_sm + (h - Hq) * D;
+      const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
+      float sn, cs;
+      sincosf(ps * inv_freq, &sn, &cs);
+      const float x1 = half_to_float<BF16>(base[i]), x2 = half_to_float<BF16>(base[i + half]);
+      base[i] = float_to_half<BF16>(x1 * cs - x2 * sn);
+      base[i + half] = float_to_half<BF16>(x2 * cs + x1 * sn);
+    }
+    return;
+  }
+  const int i = threadIdx.x % half, slot = threadIdx.x / half;
+  if (slot >= slots) return;
+  const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
+  float sn, cs;
+  sincosf(ps * inv_freq, &sn, &cs);
+  for (int h = slot; h < Hq + Hkv; h += slots) {
     uint16_t* base = h < Hq ? q + (int64_t)m * q_sm + h * D : k + (int64_t)m * k_sm + (h - Hq) * D;
-    const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
-    float sn, cs;
-    sincosf(ps * inv_freq, &sn, &cs);
     const float x1 = half_to_float<BF16>(base[i]), x2 = half_to_float<BF16>(base[i + half]);
     base[i] = float_to_half<BF16>(x1 * cs - x2 * sn);
     base[i + half] = float_to_half<BF16>(x2 * cs + x1 * sn);
@@ -320,6 +336,10 @@ extern "C" int b200_rmsnorm(const void* x, void* residual, const void* weight, v
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, B200_ERR_UNSUPPORTED, "rmsnorm: dtype");
   if (M == 0) return B200_OK;
   if (int rc = require_sm100("rmsnorm")) return rc;
+  // aligned rows: the register-resident vector kernel of fused_elem.cu without its quantiser
+  if (H % 128 == 0 && H <= 8192 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)weight & 15) == 0 && ((uintptr_t)out & 15) == 0 &&
+      (!residual || ((uintptr_t)residual & 15) == 0))
+    return b200_rmsnorm_quant_fp8(x, residual, weight, out, nullptr, 0, nullptr, 0, 0, dtype, M, H, eps, 0.f, 0.f, 0.f, stream);
   static bool cfg = false;
   if (!cfg) {
     cudaFuncSetAttribute(rmsnorm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);

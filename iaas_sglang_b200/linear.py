@@ -32,6 +32,13 @@ class Fp8BlockLinearMethod:
             out = out + bias
         return out.to(dtype=x.dtype).view(*out_shape)
 
+    def apply_quantized(self, layer, x_q: torch.Tensor, x_s: torch.Tensor, out_dtype: torch.dtype,
+                        bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """The same linear when the producer of x already emitted its group-128 quantisation
+        (ops.rmsnorm_quant_fp8 / ops.silu_and_mul_quant_fp8): fp8_utils.py:205-207 without :202-204."""
+        out = ops.fp8_blockwise_scaled_mm(x_q, layer.weight.t(), x_s, layer.weight_scale_inv.t(), out_dtype)
+        return out if bias is None else out + bias
+
 
 class W8A8Int8LinearMethod:
     """layer.weight stored as W^T view ([K,N] column-major int8), layer.weight_scale [N,1] f32 (w8a8_int8.py:88-123)."""
@@ -53,11 +60,15 @@ class AWQLinearMethod:
         return out.reshape(out_shape)
 
 
-def row_parallel_forward(method, layer, x: torch.Tensor, bias: Optional[torch.Tensor] = None,
-                         reduce_results: bool = True) -> torch.Tensor:
-    """RowParallelLinear.forward (linear.py:1360-1382): bias only on rank 0, all-reduce when tp_size > 1."""
+def row_parallel_forward(method, layer, x, bias: Optional[torch.Tensor] = None,
+                         reduce_results: bool = True, out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """RowParallelLinear.forward (linear.py:1360-1382): bias only on rank 0, all-reduce when tp_size > 1.
+    x may be an (x_q, x_s) pair from a fused quantising producer (FP8 block method only)."""
     b = bias if (bias is not None and tp.get_tensor_model_parallel_rank() == 0) else None
-    out = method.apply(layer, x, b)
+    if isinstance(x, tuple):
+        out = method.apply_quantized(layer, x[0], x[1], out_dtype, b)
+    else:
+        out = method.apply(layer, x, b)
     if reduce_results and tp.get_tensor_model_parallel_world_size() > 1:
         out = tp.tensor_model_parallel_all_reduce(out)
     return out

@@ -424,6 +424,46 @@ def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optiona
     return out
 
 
+def _fp8_group_outputs(M: int, K: int, dev) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(x_q [M,K] e4m3, x_s [M,K/128] f32 with stride(0) == 1) -- the operands fp8_blockwise_scaled_mm wants,
+    as per_token_group_quant_fp8(column_major_scales=True) lays them out."""
+    x_q = torch.empty((M, K), dtype=fp8_dtype, device=dev)
+    x_s = torch.empty((K // 128, M), dtype=torch.float32, device=dev).t()
+    return x_q, x_s
+
+
+def rmsnorm_quant_fp8(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None,
+                      quant_eps: float = 1e-10, want_half: bool = False):
+    """RMSNorm (+ in-place residual add, layernorm.py forward_cuda / fused_add_rmsnorm) fused with
+    sglang_per_token_group_quant_fp8(group 128, column-major scales): returns (x_q, x_s[, normed]) bit-identical to
+    rmsnorm() followed by per_token_group_quant_fp8()."""
+    dev = require_cuda(x, weight, residual)
+    assert x.is_contiguous() and x.dim() == 2 and x.shape[1] % 128 == 0
+    M, H = x.shape
+    x_q, x_s = _fp8_group_outputs(M, H, dev)
+    out = torch.empty_like(x) if want_half else None
+    if M > 0:
+        with torch.cuda.device(dev):
+            check(load().b200_rmsnorm_quant_fp8(ptr(x), ptr(residual), ptr(weight), ptr(out), ptr(x_q), H, ptr(x_s),
+                                                x_s.stride(0), x_s.stride(1), DTYPE_CODE[x.dtype], M, H, eps, quant_eps,
+                                                -FP8_MAX, FP8_MAX, current_stream(dev)))
+    return (x_q, x_s, out) if want_half else (x_q, x_s)
+
+
+def silu_and_mul_quant_fp8(x: torch.Tensor, quant_eps: float = 1e-10):
+    """silu_and_mul (activation.py SiluAndMul.forward_cuda) fused with the group-128 FP8 quantiser: (x_q, x_s)
+    bit-identical to silu_and_mul() followed by per_token_group_quant_fp8(column_major_scales=True)."""
+    dev = require_cuda(x)
+    assert x.is_contiguous() and x.dim() == 2 and (x.shape[1] // 2) % 128 == 0
+    M, d = x.shape[0], x.shape[1] // 2
+    x_q, x_s = _fp8_group_outputs(M, d, dev)
+    if M > 0:
+        with torch.cuda.device(dev):
+            check(load().b200_silu_mul_quant_fp8(ptr(x), ptr(x_q), d, ptr(x_s), x_s.stride(0), x_s.stride(1),
+                                                 DTYPE_CODE[x.dtype], M, d, quant_eps, -FP8_MAX, FP8_MAX, current_stream(dev)))
+    return x_q, x_s
+
+
 def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
     dev = require_cuda(x)
     assert x.is_contiguous() and x.dim() == 2

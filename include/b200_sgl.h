@@ -216,6 +216,18 @@ int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qweight, const 
 /* if residual != NULL: residual += x (stored back, half precision), then out = rmsnorm(residual)*w */
 int b200_rmsnorm(const void* x, void* residual, const void* weight, void* out, int dtype, int M, int H, float eps,
                  void* stream);
+/* Fused producers of an FP8 block-quantised linear's input:
+ *   rmsnorm_quant_fp8   = fused add + RMSNorm (sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu;
+ *                         python/sglang/srt/layers/layernorm.py) followed by sgl_per_token_group_quant_fp8
+ *                         (per_token_group_quant_8bit.cu:25-115), group 128; `out` (half result) may be NULL;
+ *                         q == NULL runs the norm alone;
+ *   silu_mul_quant_fp8  = silu_and_mul (sgl-kernel/csrc/elementwise/activation.cu) followed by the same quantiser.
+ * q / s are bit-identical to the two separate ops.  s strides as in b200_per_token_group_quant_fp8. */
+int b200_rmsnorm_quant_fp8(const void* x, void* residual, const void* weight, void* out, void* q, int64_t q_stride_m,
+                           float* s, int64_t s_stride_m, int64_t s_stride_g, int dtype, int M, int H, float eps,
+                           float quant_eps, float fp8_min, float fp8_max, void* stream);
+int b200_silu_mul_quant_fp8(const void* x, void* q, int64_t q_stride_m, float* s, int64_t s_stride_m, int64_t s_stride_g,
+                            int dtype, int M, int d, float quant_eps, float fp8_min, float fp8_max, void* stream);
 int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int d, void* stream);
 /* in-place neox-style rotary embedding on q [M,Hq,D] and k [M,Hkv,D] (heads contiguous, row strides in
  * elements: q and k may be column slices of one packed qkv tensor), positions int64 [M] */

@@ -231,3 +231,87 @@ def test_awq_fused_gemm_cfg3_shapes(M, N, K):
     # the same call again gives the same bits (fixed-order split-K reduction)
     out2 = ops.awq_w4a16_gemm(x.cuda(), qw.cuda(), sc.cuda(), qz.cuda(), bias.cuda() if bias is not None else None)
     assert torch.equal(out, out2)
+
+
+# ---- fused producers of an FP8 linear's input (fused_elem.cu) ----
+@pytest.mark.parametrize("M,H,dt,res", [(64, 4096, torch.bfloat16, True), (7, 2048, torch.bfloat16, False),
+                                        (130, 8192, torch.bfloat16, True), (33, 5120, torch.float16, True),
+                                        (1, 128, torch.bfloat16, True)])
+def test_rmsnorm_quant_fp8_is_bit_identical_to_the_two_step_path(M, H, dt, res):
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(M + H)
+    x = (torch.randn(M, H, generator=g) * 2).to(dt).cuda()
+    w = (torch.rand(H, generator=g) + 0.5).to(dt).cuda()
+    r1 = (torch.randn(M, H, generator=g)).to(dt).cuda() if res else None
+    r2 = r1.clone() if res else None
+    normed = ops.rmsnorm(x, w, 1e-5, residual=r1)
+    q_ref, s_ref = ops.per_token_group_quant_fp8(normed, 128, column_major_scales=True)
+    q, s, half = ops.rmsnorm_quant_fp8(x, w, 1e-5, residual=r2, want_half=True)
+    assert torch.equal(half.view(torch.int16), normed.view(torch.int16))
+    assert torch.equal(q.view(torch.uint8), q_ref.view(torch.uint8)) and torch.equal(s, s_ref)
+    assert s.stride(0) == 1  # column-major scales, as fp8_blockwise_scaled_mm wants them
+    if res:
+        assert torch.equal(r1.view(torch.int16), r2.view(torch.int16))
+    # and the norm itself against the oracle (layernorm.py forward_native)
+    xs = x.float().cpu() + (r1.float().cpu() - x.float().cpu() if False else 0)
+    base = r1.float().cpu() if res else x.float().cpu()   # r1 now holds x + residual
+    ref = base * torch.rsqrt(base.pow(2).mean(-1, keepdim=True) + 1e-5)
+    ref = ref.to(dt).float() * w.float().cpu()
+    assert rel_l2(normed.float().cpu(), ref) < 3e-3
+
+
+@pytest.mark.parametrize("M,d,dt", [(64, 14336, torch.bfloat16), (5, 128, torch.bfloat16), (129, 3584, torch.float16)])
+def test_silu_mul_quant_fp8_is_bit_identical_to_the_two_step_path(M, d, dt):
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(M + d)
+    x = (torch.randn(M, 2 * d, generator=g) * 3).to(dt).cuda()
+    act = ops.silu_and_mul(x)
+    q_ref, s_ref = ops.per_token_group_quant_fp8(act, 128, column_major_scales=True)
+    q, s = ops.silu_and_mul_quant_fp8(x)
+    assert torch.equal(q.view(torch.uint8), q_ref.view(torch.uint8)) and torch.equal(s, s_ref)
+
+
+def test_fp8_linear_with_prequantised_input_equals_apply():
+    from iaas_sglang_b200 import linear, ops
+
+    class L:  # the parameter names Fp8LinearMethod creates (fp8.py:236-300)
+        pass
+
+    g = torch.Generator().manual_seed(5)
+    M, K, N = 64, 4096, 6144
+    layer = L()
+    layer.weight = (torch.randn(N, K, generator=g) * 30).clamp(-448, 448).to(torch.float8_e4m3fn).cuda()
+    layer.weight_scale_inv = (torch.rand(N // 128, K // 128, generator=g) * 1e-2 + 1e-3).cuda()
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).cuda()
+    w = torch.ones(K, dtype=torch.bfloat16).cuda()
+    m = linear.Fp8BlockLinearMethod()
+    a = m.apply(layer, ops.rmsnorm(x, w, 1e-5))
+    xq, xs = ops.rmsnorm_quant_fp8(x, w, 1e-5)
+    b = m.apply_quantized(layer, xq, xs, torch.bfloat16)
+    assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (10, 2, 128), (32, 8, 64), (3, 1, 80)])
+def test_rope_neox_against_forward_native(Hq, Hkv, D):
+    """rotary_embedding.py forward_native (is_neox_style): x1' = x1 cos - x2 sin, x2' = x2 cos + x1 sin."""
+    from iaas_sglang_b200 import ops
+
+    g = torch.Generator().manual_seed(Hq + D)
+    M = 37
+    qkv = torch.randn(M, (Hq + 2 * Hkv) * D, generator=g).to(torch.bfloat16).cuda()
+    q, k, _ = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    pos = torch.randint(0, 8192, (M,), generator=g, dtype=torch.int64).cuda()
+    q0, k0 = q.float().cpu().view(M, Hq, D), k.float().cpu().view(M, Hkv, D)
+    ops.rope_neox_(q, k, pos, D, 500000.0)
+    inv = 1.0 / (500000.0 ** (torch.arange(0, D, 2).float() / D))
+    ang = pos.cpu().float()[:, None] * inv[None]
+    cs, sn = ang.cos()[:, None, :], ang.sin()[:, None, :]
+
+    def rot(t):
+        x1, x2 = t[..., : D // 2], t[..., D // 2:]
+        return torch.cat([x1 * cs - x2 * sn, x2 * cs + x1 * sn], -1)
+
+    assert rel_l2(q.float().cpu().view(M, Hq, D), rot(q0)) < 6e-3
+    assert rel_l2(k.float().cpu().view(M, Hkv, D), rot(k0)) < 6e-3

@@ -587,6 +587,10 @@ def main():
             "step_roofline": {"algorithmic_bytes_per_step_per_gpu": int(step_bytes), "hbm_time_ms_at_peak": round(step_bytes / peak / 1e6, 4),
                               "frac": round(step_bytes / peak / 1e6 / ms, 4)},
         }
+        if world > 1:
+            car = tpmod.custom_all_reduce()
+            line["config"]["allreduce"] = ("one-shot NVLink peer-memory kernel (csrc/allreduce.cu), error word %d" % car.error()
+                                           if car is not None else "ncclAllReduce")
         if not args.no_cpu_baseline and world == 1 and wl["quant"] == "fp8":
             try:
                 cores = os.cpu_count() or 1

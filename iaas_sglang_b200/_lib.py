@@ -100,6 +100,12 @@ SIGNATURES = {
     "b200_silu_and_mul": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_rope_neox": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float,
                              c_void_p]),
+    "b200_ar_region_bytes": (c_size_t, [c_size_t]),
+    "b200_ar_alloc": (c_int, [c_size_t, C.POINTER(c_void_p), c_void_p]),
+    "b200_ar_init": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, C.POINTER(c_void_p)]),
+    "b200_ar_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "b200_ar_error": (c_int, [c_void_p]),
+    "b200_ar_destroy": (None, [c_void_p]),
 }
 
 _lib: Optional[C.CDLL] = None

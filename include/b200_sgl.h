@@ -234,6 +234,23 @@ int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int d, void* s
 int b200_rope_neox(void* q, int64_t q_stride_m, void* k, int64_t k_stride_m, const int64_t* positions, int dtype, int M,
                    int Hq, int Hkv, int D, float theta, void* stream);
 
+/* --------------------------------------------------------------------------------------------
+ * One-shot all-reduce(sum) over NVLink peer memory for the row-parallel linears' outputs.
+ * Replaces the custom P2P all-reduce of sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:203-456 /
+ * python/sglang/srt/distributed/device_communicators/custom_all_reduce.py:148,414-480 (call site
+ * communication_op.py:11-13).  One process per GPU: every rank allocates a region (b200_ar_alloc), the 64-byte
+ * CUDA-IPC handles are exchanged by the host (torch.distributed all_gather), b200_ar_init opens the peers'.
+ * b200_ar_allreduce launches ONE kernel on `stream` (no host sync, CUDA-graph capturable); every rank must call
+ * it with the same n_elems in the same order.  Results are bit-identical on all ranks (sum in rank order, fp32).
+ * b200_ar_error returns 1 if a peer never arrived (the kernel gave up after ~20 s instead of hanging).
+ * ------------------------------------------------------------------------------------------ */
+size_t b200_ar_region_bytes(size_t max_message_bytes);
+int b200_ar_alloc(size_t max_message_bytes, void** region_out, void* ipc_handle_out64);
+int b200_ar_init(void* own_region, const void* handles, int rank, int world, size_t max_message_bytes, void** ctx_out);
+int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int dtype, void* stream);
+int b200_ar_error(void* ctx);
+void b200_ar_destroy(void* ctx);
+
 #ifdef __cplusplus
 }
 #endif

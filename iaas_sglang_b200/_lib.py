@@ -104,6 +104,7 @@ SIGNATURES = {
     "b200_ar_alloc": (c_int, [c_size_t, C.POINTER(c_void_p), c_void_p]),
     "b200_ar_init": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, C.POINTER(c_void_p)]),
     "b200_ar_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "b200_ar_mode": (c_int, [c_int, c_size_t]),
     "b200_ar_error": (c_int, [c_void_p]),
     "b200_ar_destroy": (None, [c_void_p]),
 }

@@ -6,7 +6,8 @@
 // Larger messages and anything this path rejects stay on ncclAllReduce (tp.py).
 //
 // Every rank owns one cudaMalloc'ed region, opened by its peers through CUDA IPC:
-//   [flags: MAX_BLOCKS x 8 uint32, written by PEERS] [counters: MAX_BLOCKS uint32, private] [err] [data slot 0] [data slot 1]
+//   [flags: MAX_BLOCKS x 8 uint32, written by PEERS] [flag sequence + call counters: per block, private] [err]
+//   [data slot 0] [data slot 1]
 // One kernel per all-reduce, grid = nblocks (<= MAX_BLOCKS), no host synchronisation, CUDA-graph capturable:
 //   1. block b copies its chunk of the input into the rank's own data slot (slot = call parity);
 //   2. block b tells block b of every peer "my chunk of call n is in place" (st.release.sys into the peer's flag
@@ -17,6 +18,7 @@
 // an end-of-call barrier unnecessary: a rank can only start call n + 2 (same slot as n) after it passed the barrier of
 // call n + 1, which every peer signals only after finishing call n.  A spin that lasts longer than ~20 s sets an
 // error word and lets the kernel finish (wrong data, no hang); the host checks it with b200_ar_error().
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -29,7 +31,9 @@ constexpr int AR_THREADS = 512;
 constexpr size_t AR_FLAG_BYTES = AR_MAX_BLOCKS * AR_MAX_RANKS * 4;  // 4 KB
 constexpr size_t AR_CNT_OFF = AR_FLAG_BYTES;
 constexpr size_t AR_ERR_OFF = AR_CNT_OFF + AR_MAX_BLOCKS * 4;
+constexpr size_t AR_CALLS_OFF = AR_ERR_OFF + 64;  // per-block number of calls (its parity picks the data slot)
 constexpr size_t AR_DATA_OFF = 8192;
+static_assert(AR_CALLS_OFF + AR_MAX_BLOCKS * 4 <= AR_DATA_OFF, "region header");
 
 struct ArParams {
   uint8_t* base[AR_MAX_RANKS];  // region of every rank (own = local pointer, peers = IPC mappings)
@@ -71,8 +75,9 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_oneshot_kernel(const __g
   const int b = blockIdx.x;
   uint8_t* mine = p.base[p.rank];
   uint32_t* cnt = reinterpret_cast<uint32_t*>(mine + AR_CNT_OFF) + b;
-  const uint32_t call = *cnt + 1;  // this block's call number (private to the block, bumped at the end)
-  const int slot = call & 1;
+  uint32_t* calls = reinterpret_cast<uint32_t*>(mine + AR_CALLS_OFF) + b;
+  const uint32_t call = *cnt + 1;  // this block's flag sequence number (private to the block, bumped at the end)
+  const int slot = *calls & 1;     // consecutive calls (of either kernel) alternate between the two data slots
   const int64_t per = (p.nvec + gridDim.x - 1) / gridDim.x;
   const int64_t v0 = (int64_t)b * per, v1 = v0 + per < p.nvec ? v0 + per : p.nvec;
 
@@ -111,7 +116,89 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_oneshot_kernel(const __g
     p.out[i] = make_uint4(pack_half2<BF16>(acc[0], acc[1]), pack_half2<BF16>(acc[2], acc[3]), pack_half2<BF16>(acc[4], acc[5]),
                           pack_half2<BF16>(acc[6], acc[7]));
   }
-  if (threadIdx.x == 0) *cnt = call;
+  if (threadIdx.x == 0) {
+    *cnt = call;
+    *calls = *calls + 1;
+  }
+}
+
+// Two-shot variant for more ranks / larger messages (custom_all_reduce.cuh:300-400 picks the same way): rank r
+// reduces only chunk r (1/W of the message) from every rank, publishes it in place in its own slot, and all ranks
+// gather the W reduced chunks: 2 (W-1)/W of the message crosses NVLink per rank instead of (W-1) times the message.
+// Block b owns sub-range b of EVERY chunk in all three phases, so the per-block flag barrier still covers exactly
+// the data the block depends on.  Two barriers per call, two consecutive flag sequence numbers.
+template <int WORLD>
+__device__ __forceinline__ void ar_block_barrier(const ArParams& p, uint8_t* mine, int b, uint32_t value) {
+  if (threadIdx.x < WORLD && threadIdx.x != p.rank) {
+    const int peer = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(p.base[peer]) + b * AR_MAX_RANKS + p.rank, value);
+    const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine) + b * AR_MAX_RANKS + peer;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(flag) - value) < 0) {
+      if (clock64() - t0 > 40000000000LL) {
+        *reinterpret_cast<uint32_t*>(mine + AR_ERR_OFF) = 1;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+template <bool BF16, int WORLD>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_twoshot_kernel(const __grid_constant__ ArParams p) {
+  const int b = blockIdx.x;
+  uint8_t* mine = p.base[p.rank];
+  uint32_t* cnt = reinterpret_cast<uint32_t*>(mine + AR_CNT_OFF) + b;
+  uint32_t* calls = reinterpret_cast<uint32_t*>(mine + AR_CALLS_OFF) + b;
+  const uint32_t call = *cnt + 1;  // two barriers per call: flag values call and call + 1
+  const int slot = *calls & 1;
+  const int64_t cv = (p.nvec + WORLD - 1) / WORLD;          // vectors per chunk
+  const int64_t sv = (cv + gridDim.x - 1) / gridDim.x;      // vectors per (chunk, block)
+  const int64_t j0 = (int64_t)b * sv, j1 = j0 + sv < cv ? j0 + sv : cv;
+  uint4* my_slot = reinterpret_cast<uint4*>(mine + AR_DATA_OFF + slot * p.slot_bytes);
+  // 1. my input, sub-range b of every chunk -> my slot
+#pragma unroll
+  for (int c = 0; c < WORLD; ++c)
+    for (int64_t j = j0 + threadIdx.x; j < j1; j += AR_THREADS) {
+      const int64_t i = c * cv + j;
+      if (i < p.nvec) my_slot[i] = p.in[i];
+    }
+  __syncthreads();
+  ar_block_barrier<WORLD>(p, mine, b, call);
+  // 2. reduce chunk `rank` in rank order, publish it in place
+  const uint4* src[WORLD];
+#pragma unroll
+  for (int r = 0; r < WORLD; ++r) src[r] = reinterpret_cast<const uint4*>(p.base[r] + AR_DATA_OFF + slot * p.slot_bytes);
+  for (int64_t j = j0 + threadIdx.x; j < j1; j += AR_THREADS) {
+    const int64_t i = p.rank * cv + j;
+    if (i >= p.nvec) break;
+    uint4 v[WORLD];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) v[r] = ld_volatile_v4(src[r] + i);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) add8<BF16>(acc, v[r]);
+    const uint4 o = make_uint4(pack_half2<BF16>(acc[0], acc[1]), pack_half2<BF16>(acc[2], acc[3]),
+                               pack_half2<BF16>(acc[4], acc[5]), pack_half2<BF16>(acc[6], acc[7]));
+    my_slot[i] = o;
+    p.out[i] = o;
+  }
+  __syncthreads();
+  ar_block_barrier<WORLD>(p, mine, b, call + 1);
+  // 3. gather the other ranks' reduced chunks
+#pragma unroll
+  for (int c = 0; c < WORLD; ++c) {
+    if (c == p.rank) continue;
+    for (int64_t j = j0 + threadIdx.x; j < j1; j += AR_THREADS) {
+      const int64_t i = c * cv + j;
+      if (i < p.nvec) p.out[i] = ld_volatile_v4(src[c] + i);
+    }
+  }
+  if (threadIdx.x == 0) {
+    *cnt = call + 1;
+    *calls = *calls + 1;
+  }
 }
 
 struct ArContext {
@@ -199,6 +286,18 @@ extern "C" void b200_ar_destroy(void* ctx) {
   delete c;
 }
 
+// Which path is fastest for a message, measured on 2 / 4 / 8 B200 of one NVSwitch box (tools/ar_check.py AR_SWEEP=1,
+// profiles/r01b_allreduce.md): 1 = one-shot, 2 = two-shot, 0 = leave it to ncclAllReduce.  The reference makes the same
+// kind of split (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one stage, else two).
+extern "C" int b200_ar_mode(int world, size_t bytes) {
+  if (world < 2 || world > AR_MAX_RANKS) return 0;
+  if (world == 2) return 1;
+  if (world <= 4) return bytes <= ((size_t)6 << 20) ? 1 : 2;
+  if (bytes <= (size_t)1536 * 1024) return 1;
+  if (bytes < ((size_t)3 << 20)) return 0;
+  return 2;
+}
+
 // in / out: n_elems 16-bit values, 16-byte aligned, n_elems % 8 == 0, n_elems * 2 <= max_message_bytes; out may alias in
 extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int dtype, void* stream) {
   ArContext* c = (ArContext*)ctx;
@@ -218,6 +317,32 @@ extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n
   if (nb > AR_MAX_BLOCKS) nb = AR_MAX_BLOCKS;
   if (nb < 1) nb = 1;
   cudaStream_t st = (cudaStream_t)stream;
+  // a function of (world, size) only, so every rank picks the same kernel
+  bool two_shot = b200_ar_mode(p.world, (size_t)n_elems * 2) == 2;
+  {
+    static int mode = -1;  // developer override: B200_AR_MODE=1 one-shot, 2 two-shot (must be the same on every rank)
+    if (mode < 0) { const char* e = getenv("B200_AR_MODE"); mode = e ? atoi(e) : 0; }
+    if (mode == 1) two_shot = false;
+    if (mode == 2 && p.world > 2) two_shot = true;
+  }
+  if (two_shot) {
+    int64_t nb2 = ((p.nvec + p.world - 1) / p.world + AR_THREADS - 1) / AR_THREADS;
+    if (nb2 > AR_MAX_BLOCKS) nb2 = AR_MAX_BLOCKS;
+    if (nb2 < 1) nb2 = 1;
+#define B200_AR2(W)                                                                                      \
+  case W:                                                                                                \
+    if (dtype == B200_BF16) allreduce_twoshot_kernel<true, W><<<(unsigned)nb2, AR_THREADS, 0, st>>>(p);  \
+    else allreduce_twoshot_kernel<false, W><<<(unsigned)nb2, AR_THREADS, 0, st>>>(p);                    \
+    break;
+    switch (p.world) {
+      B200_AR2(3) B200_AR2(4) B200_AR2(5) B200_AR2(6) B200_AR2(7) B200_AR2(8)
+      default:
+        set_error("ar_allreduce: world %d", p.world);
+        return B200_ERR_UNSUPPORTED;
+    }
+#undef B200_AR2
+    return launched("allreduce_twoshot_kernel launch");
+  }
 #define B200_AR(W)                                                                        \
   case W:                                                                                 \
     if (dtype == B200_BF16) allreduce_oneshot_kernel<true, W><<<(unsigned)nb, AR_THREADS, 0, st>>>(p); \

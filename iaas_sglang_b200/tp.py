@@ -58,7 +58,7 @@ class CustomAllReduce:
         """custom_all_reduce.py:414-436: dtype / size / alignment gate."""
         n = t.numel() * t.element_size()
         return (t.is_cuda and t.dtype in (torch.bfloat16, torch.float16) and t.is_contiguous() and n <= self.max_bytes
-                and t.numel() % 8 == 0 and t.data_ptr() % 16 == 0)
+                and t.numel() % 8 == 0 and t.data_ptr() % 16 == 0 and self.lib.b200_ar_mode(self.world, n) != 0)
 
     def all_reduce_(self, t: torch.Tensor) -> torch.Tensor:
         from .ops import DTYPE_CODE, check, current_stream

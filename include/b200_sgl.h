@@ -248,6 +248,8 @@ size_t b200_ar_region_bytes(size_t max_message_bytes);
 int b200_ar_alloc(size_t max_message_bytes, void** region_out, void* ipc_handle_out64);
 int b200_ar_init(void* own_region, const void* handles, int rank, int world, size_t max_message_bytes, void** ctx_out);
 int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int dtype, void* stream);
+/* 1 = one-shot kernel, 2 = two-shot kernel, 0 = ncclAllReduce is faster for this (world, message size) */
+int b200_ar_mode(int world, size_t bytes);
 int b200_ar_error(void* ctx);
 void b200_ar_destroy(void* ctx);
 

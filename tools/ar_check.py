@@ -54,6 +54,17 @@ def main():
         ar.all_reduce_(y)
     torch.cuda.synchronize()
     ok = ok and bool((y == want).all().item())
+    # one-shot and two-shot calls interleaved (they share the flags and the two data slots)
+    small = torch.full((4096,), float(rank + 1), device=dev, dtype=torch.bfloat16)
+    big = torch.full((2 << 20,), float(rank + 1), device=dev, dtype=torch.bfloat16)
+    for i in range(60):
+        a, c = small.clone(), big.clone()
+        ar.all_reduce_(a)
+        ar.all_reduce_(c)
+        if i % 3 == 0:
+            ar.all_reduce_(a.copy_(small))
+    torch.cuda.synchronize()
+    ok = ok and bool((a == want).all().item()) and bool((c == want).all().item())
     st = torch.cuda.Stream()
     buf = x.clone()
     with torch.cuda.stream(st):
@@ -93,7 +104,10 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item() * 1e3
 
-    for name, n in (("cfg2 tp%d 64xN x4096" % world, 64 * world * 4096), ("cfg3 128x5120", 128 * 5120), ("cfg4 256x8192", 256 * 8192)):
+    cases = [("cfg2 tp%d 64xN x4096" % world, 64 * world * 4096), ("cfg3 128x5120", 128 * 5120), ("cfg4 256x8192", 256 * 8192)]
+    if os.environ.get("AR_SWEEP"):
+        cases = [(f"{kb} KB", kb * 512) for kb in (64, 256, 512, 1024, 2048, 4096, 8192)]
+    for name, n in cases:
         t = torch.randn(n, device=dev, dtype=torch.bfloat16)
         us_c = timeit(lambda a: ar.all_reduce_(a), t)
         us_n = timeit(lambda a: dist.all_reduce(a), t)

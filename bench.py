@@ -562,6 +562,14 @@ def main():
         e2e_ms = e2e_max if e2e_ms is not None else None
         achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
 
+    traffic = None
+    try:   # per-launch DRAM bytes of the same kernel at the same shape, from the committed ncu capture
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            ent = json.load(f).get(f"{args.workload}/tp{tp}")
+        if ent and batch == wl["batch"] * tp and n_layers > 0:
+            traffic = int(ent["bytes"])
+    except (OSError, ValueError, KeyError):
+        traffic = None
     if rank == 0:
         value = batch / (ms * 1e-3)
         step_bytes = n_layers * (stack.attn_bytes_per_layer() + stack.weight_bytes_per_layer())
@@ -581,7 +589,7 @@ def main():
             "clocks": clk,
             "roofline": {
                 "kernel": "decode_attn_mma_kernel (+ split merge)", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
-                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "ms_per_launch": round(attn_ms, 4), "algorithmic_bytes_per_launch": attn_bytes,
                 "frac_of_nominal_8TBs": round(achieved / 8000.0, 4)},
             "step_roofline": {"algorithmic_bytes_per_step_per_gpu": int(step_bytes), "hbm_time_ms_at_peak": round(step_bytes / peak / 1e6, 4),

@@ -186,13 +186,20 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_twoshot_kernel(const __g
   }
   __syncthreads();
   ar_block_barrier<WORLD>(p, mine, b, call + 1);
-  // 3. gather the other ranks' reduced chunks
+  // 3. gather the other ranks' reduced chunks: all W - 1 remote loads of a thread are issued before the first store
+  //    (volatile loads are not reordered across the stores by the compiler: chunk by chunk they were W - 1 serial
+  //    NVLink round trips)
+  for (int64_t j = j0 + threadIdx.x; j < j1; j += AR_THREADS) {
+    uint4 v[WORLD];
 #pragma unroll
-  for (int c = 0; c < WORLD; ++c) {
-    if (c == p.rank) continue;
-    for (int64_t j = j0 + threadIdx.x; j < j1; j += AR_THREADS) {
+    for (int c = 0; c < WORLD; ++c) {
       const int64_t i = c * cv + j;
-      if (i < p.nvec) p.out[i] = ld_volatile_v4(src[c] + i);
+      if (c != p.rank && i < p.nvec) v[c] = ld_volatile_v4(src[c] + i);
+    }
+#pragma unroll
+    for (int c = 0; c < WORLD; ++c) {
+      const int64_t i = c * cv + j;
+      if (c != p.rank && i < p.nvec) p.out[i] = v[c];
     }
   }
   if (threadIdx.x == 0) {

@@ -162,7 +162,7 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    for (int a = 0; a < AQ_NA; ++a) mbar_init(&afull[a], TEAM);
+    for (int a = 0; a < AQ_NA; ++a) mbar_init(&afull[a], TEAM / 32);  // one arrival per dequantiser warp
     for (int g = 0; g < RB; ++g) mbar_init(&gfree[g], 1);
     mbar_init(tfull, 1);
     mbar_init(xbar, 1);
@@ -272,7 +272,8 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
             aq_dequant_item<BF>(reinterpret_cast<const uint32_t*>(st + u * AQ_RAW), smem + (a * NT + u) * (AQ_BN * AQ_BK), c, ko, h, zp[it], s2[it]);
         }
         fence_proxy_async();  // generic-proxy stores -> read by the tensor core through the async proxy
-        mbar_arrive(&afull[a]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&afull[a]);
       }
     }
     mbar_wait(tfull, 0);

@@ -203,7 +203,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
     }
     for (int a = 0; a < NBUF; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], NE);
+      mbar_init(&tempty[a], NE / 32);  // one arrival per epilogue WARP (512 per-thread arrivals on one barrier serialise)
     }
     mbar_init(xbar, 1);
     fence_mbar_init();
@@ -315,7 +315,8 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
             tmem_ld_32x32(lane_addr + a * BUFCOLS, r);
             tmem_ld_wait();
             tc_fence_before();
-            mbar_arrive(&tempty[a]);  // the values are in registers: the tensor core may refill the buffer
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[a]);  // the values are in registers: the tensor core may refill the buffer
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               const float4 s4 = *reinterpret_cast<const float4*>(sv + j);
@@ -342,7 +343,8 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
               }
             }
             tc_fence_before();
-            mbar_arrive(&tempty[a]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[a]);
           }
         }
       }

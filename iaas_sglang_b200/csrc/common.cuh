@@ -24,6 +24,26 @@ int device_sm_count();
 // cudaLaunchAttributeProgrammaticStreamSerialization and order themselves with griddepcontrol.wait
 bool pdl_enabled();
 
+#ifdef __CUDACC__
+// Launch `kern` as a programmatic dependent of the previous kernel of the stream (plain launch with B200_PDL=0).
+// Contract for every kernel launched this way: griddep_wait() comes before its first global-memory access, so
+// all it overlaps with its predecessor is launch latency, block scheduling and its shared-memory prologue.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 #define B200_REQUIRE(cond, code, ...)  \
   do {                                 \
     if (!(cond)) {                     \

@@ -156,6 +156,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
   const int NG = (p.Hkv / HPC) * n_qblk;
 
   // ---- batch tables + barriers ----
+  griddep_wait();    // programmatic dependent launch: q / k_new / the batch tensors belong to the stream order
+  griddep_launch();  // the merge kernel may be scheduled as soon as SM resources free up
   for (int b = threadIdx.x; b < p.B; b += kAttnThreads) {
     int64_t len = p.seq_lens[b];
     if (len < 0) len = 0;
@@ -528,6 +530,8 @@ __global__ void __launch_bounds__(128) decode_merge_part_kernel(const float* __r
                                                                 const int64_t* __restrict__ seq_lens, int B, int Hq,
                                                                 int Ggrp, int HPC, int tile_t, int NG, int n_qblk,
                                                                 int grid, int Dv) {
+  griddep_wait();
+  griddep_launch();
   const int b = blockIdx.x / Hq, h = blockIdx.x - b * Hq;
   __shared__ int red[2][4];
   int all = 0, before = 0, mine = 0;
@@ -783,10 +787,10 @@ static int launch_mma(const DecodeKParams& kp, cudaStream_t st) {
     configured = true;
   }
   const int grid = attn_grid();
-  kern<<<grid, kAttnThreads, C::SMEM_BYTES, st>>>(kp);
+  launch_pdl(kern, dim3(grid), dim3(kAttnThreads), C::SMEM_BYTES, st, kp);
   if (int rc = launched("decode_attn_mma_kernel launch")) return rc;
   const int n_qblk = (kp.G + 15) / 16;
-  decode_merge_part_kernel<BF16><<<kp.B * kp.Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq,
+  launch_pdl(decode_merge_part_kernel<BF16>, dim3(kp.B * kp.Hq), dim3(128), 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq,
                                                                kp.G, HPC, C::TILE_T, (kp.Hkv / HPC) * n_qblk, n_qblk, grid,
                                                                kp.Dv);
   return launched("decode_merge_part_kernel launch");

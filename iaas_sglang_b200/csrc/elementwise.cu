@@ -43,6 +43,8 @@ __global__ void __launch_bounds__(256) group_quant_fp8_kernel(const uint16_t* __
                                                               uint8_t* __restrict__ q, int64_t q_sm,
                                                               float* __restrict__ s, int64_t s_sm, int64_t s_sg, int M,
                                                               int groups_per_row, float eps, float fmin_, float fmax_) {
+  griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
+  griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int64_t gid = (int64_t)blockIdx.x * 16 + (threadIdx.x >> 4);
   const int sub = threadIdx.x & 15;
   if (gid >= (int64_t)M * groups_per_row) return;
@@ -157,6 +159,8 @@ template <bool BF16>
 __global__ void __launch_bounds__(256) rmsnorm_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ residual,
                                                       const uint16_t* __restrict__ w, uint16_t* __restrict__ out, int H,
                                                       float eps) {
+  griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
+  griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int64_t m = blockIdx.x;
   extern __shared__ float row[];
   __shared__ float red[8];
@@ -188,6 +192,8 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(const uint16_t* __restrict
 template <bool BF16>
 __global__ void __launch_bounds__(256) silu_mul_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ out,
                                                        int64_t M, int d) {
+  griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
+  griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;  // over M * d/8 vectors
   const int dv = d / 8;
   if (i >= M * dv) return;
@@ -211,6 +217,8 @@ __global__ void __launch_bounds__(256) silu_mul_kernel(const uint16_t* __restric
 template <bool BF16>
 __global__ void rope_neox_kernel(uint16_t* __restrict__ q, int64_t q_sm, uint16_t* __restrict__ k, int64_t k_sm,
                                  const int64_t* __restrict__ pos, int Hq, int Hkv, int D, float log2_theta) {
+  griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
+  griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int m = blockIdx.x;
   const int half = D / 2;
   const float ps = (float)pos[m];
@@ -289,9 +297,9 @@ extern "C" int b200_per_token_group_quant_fp8(const void* x, int64_t x_sm, int x
   if (fast) {
     const unsigned blocks = (unsigned)((ngroups + 15) / 16);
     if (x_dtype == B200_BF16)
-      group_quant_fp8_kernel<true><<<blocks, 256, 0, st>>>((const uint16_t*)x, x_sm, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, gpr, eps, fp8_min, fp8_max);
+      launch_pdl(group_quant_fp8_kernel<true>, dim3(blocks), dim3(256), 0, st, (const uint16_t*)x, x_sm, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, gpr, eps, fp8_min, fp8_max);
     else
-      group_quant_fp8_kernel<false><<<blocks, 256, 0, st>>>((const uint16_t*)x, x_sm, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, gpr, eps, fp8_min, fp8_max);
+      launch_pdl(group_quant_fp8_kernel<false>, dim3(blocks), dim3(256), 0, st, (const uint16_t*)x, x_sm, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, gpr, eps, fp8_min, fp8_max);
   } else {
     const unsigned blocks = (unsigned)((ngroups + 7) / 8);
     if (x_dtype == B200_BF16)
@@ -347,9 +355,9 @@ extern "C" int b200_rmsnorm(const void* x, void* residual, const void* weight, v
     cfg = true;
   }
   if (dtype == B200_BF16)
-    rmsnorm_kernel<true><<<M, 256, H * 4, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, (uint16_t*)out, H, eps);
+    launch_pdl(rmsnorm_kernel<true>, dim3(M), dim3(256), H * 4, (cudaStream_t)stream, (const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, (uint16_t*)out, H, eps);
   else
-    rmsnorm_kernel<false><<<M, 256, H * 4, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, (uint16_t*)out, H, eps);
+    launch_pdl(rmsnorm_kernel<false>, dim3(M), dim3(256), H * 4, (cudaStream_t)stream, (const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, (uint16_t*)out, H, eps);
   return launched("rmsnorm_kernel launch");
 }
 
@@ -361,9 +369,9 @@ extern "C" int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int
   const int64_t n = (int64_t)M * (d / 8);
   const unsigned blocks = (unsigned)((n + 255) / 256);
   if (dtype == B200_BF16)
-    silu_mul_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)out, M, d);
+    launch_pdl(silu_mul_kernel<true>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const uint16_t*)x, (uint16_t*)out, M, d);
   else
-    silu_mul_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, (uint16_t*)out, M, d);
+    launch_pdl(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const uint16_t*)x, (uint16_t*)out, M, d);
   return launched("silu_mul_kernel launch");
 }
 
@@ -374,8 +382,8 @@ extern "C" int b200_rope_neox(void* q, int64_t q_sm, void* k, int64_t k_sm, cons
   if (M == 0) return B200_OK;
   if (int rc = require_sm100("rope_neox")) return rc;
   if (dtype == B200_BF16)
-    rope_neox_kernel<true><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
+    launch_pdl(rope_neox_kernel<true>, dim3(M), dim3(256), 0, (cudaStream_t)stream, (uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
   else
-    rope_neox_kernel<false><<<M, 256, 0, (cudaStream_t)stream>>>((uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
+    launch_pdl(rope_neox_kernel<false>, dim3(M), dim3(256), 0, (cudaStream_t)stream, (uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
   return launched("rope_neox_kernel launch");
 }

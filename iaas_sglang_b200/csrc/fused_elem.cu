@@ -44,6 +44,8 @@ __global__ void __launch_bounds__(256) rmsnorm_quant_fp8_kernel(const uint16_t* 
                                                                 uint8_t* __restrict__ q, int64_t q_sm, float* __restrict__ s,
                                                                 int64_t s_sm, int64_t s_sg, int H, float eps, float q_eps,
                                                                 float fmin_, float fmax_) {
+  griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
+  griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int64_t m = blockIdx.x;
   const int nvec = H >> 3;
   __shared__ float red[8];
@@ -122,6 +124,8 @@ __global__ void __launch_bounds__(256) silu_mul_quant_fp8_kernel(const uint16_t*
                                                                  int64_t q_sm, float* __restrict__ s, int64_t s_sm,
                                                                  int64_t s_sg, int64_t M, int d, float q_eps, float fmin_,
                                                                  float fmax_) {
+  griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
+  griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   const int dv = d / 8;
   if (i >= M * dv) return;  // (whole 16-thread groups leave together: dv % 16 == 0)
@@ -163,7 +167,7 @@ extern "C" int b200_rmsnorm_quant_fp8(const void* x, void* residual, const void*
   cudaStream_t st = (cudaStream_t)stream;
   const int nv = (H / 8 + 255) / 256;
 #define B200_RQ(BF, NV)                                                                                                   \
-  rmsnorm_quant_fp8_kernel<BF, NV><<<M, 256, 0, st>>>((const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, \
+  launch_pdl(rmsnorm_quant_fp8_kernel<BF, NV>, dim3(M), dim3(256), 0, st, (const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, \
                                                       (uint16_t*)out, (uint8_t*)q, q_sm, s, s_sm, s_sg, H, eps, q_eps,   \
                                                       fp8_min, fp8_max)
   if (dtype == B200_BF16) {
@@ -188,8 +192,8 @@ extern "C" int b200_silu_mul_quant_fp8(const void* x, void* q, int64_t q_sm, flo
   const int64_t n = (int64_t)M * (d / 8);
   const unsigned blocks = (unsigned)((n + 255) / 256);
   if (dtype == B200_BF16)
-    silu_mul_quant_fp8_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, d, q_eps, fp8_min, fp8_max);
+    launch_pdl(silu_mul_quant_fp8_kernel<true>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const uint16_t*)x, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, d, q_eps, fp8_min, fp8_max);
   else
-    silu_mul_quant_fp8_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, d, q_eps, fp8_min, fp8_max);
+    launch_pdl(silu_mul_quant_fp8_kernel<false>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const uint16_t*)x, (uint8_t*)q, q_sm, s, s_sm, s_sg, M, d, q_eps, fp8_min, fp8_max);
   return launched("silu_mul_quant_fp8_kernel launch");
 }

@@ -522,9 +522,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
 }
 
 // merge of the units that more than one CTA worked on (decode.cpp:812-860 decode_accumulate_kv_splits;
-// decode_attention.py:492-552 _fwd_kernel_stage2).  grid = B*Hq, block = 128.  Recomputes the partition.
-template <bool BF16>
-__global__ void __launch_bounds__(128) decode_merge_part_kernel(const float* __restrict__ part_o,
+// decode_attention.py:492-552 _fwd_kernel_stage2).  One WARP per (request, head): grid = B * ceil(Hq / 8) CTAs of
+// 8 warps, a lane owns 4 consecutive output columns of every 128.  Warps are independent -- no shared memory, no
+// block barrier: each one recomputes the partition from seq_lens, keeps its (row, weight) pairs in registers and
+// hands them round with shuffles.  NV = ceil(Dv / 128).
+template <bool BF16, int NV>
+__global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __restrict__ part_o,
                                                                 const float* __restrict__ part_lse,
                                                                 uint16_t* __restrict__ out,
                                                                 const int64_t* __restrict__ seq_lens, int B, int Hq,
@@ -532,36 +535,28 @@ __global__ void __launch_bounds__(128) decode_merge_part_kernel(const float* __r
                                                                 int grid, int Dv) {
   griddep_wait();
   griddep_launch();
-  const int b = blockIdx.x / Hq, h = blockIdx.x - b * Hq;
-  __shared__ int red[2][4];
-  int all = 0, before = 0, mine = 0;
-  for (int i = threadIdx.x; i < B; i += 128) {
+  const int lane = threadIdx.x & 31;
+  const int hblocks = (Hq + 7) >> 3;
+  const int b = blockIdx.x / hblocks, h = (blockIdx.x - b * hblocks) * 8 + (threadIdx.x >> 5);
+  if (h >= Hq) return;
+  int all = 0, before = 0, tiles_b = 0;
+  for (int i = lane; i < B; i += 32) {
     int64_t len = seq_lens[i];
     if (len < 0) len = 0;
     const int tl = (int)((len + tile_t - 1) / tile_t);
     all += tl;
     if (i < b) before += tl;
-    if (i == b) mine = tl;
+    if (i == b) tiles_b = tl;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     all += __shfl_xor_sync(0xffffffffu, all, o);
     before += __shfl_xor_sync(0xffffffffu, before, o);
-    mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    tiles_b += __shfl_xor_sync(0xffffffffu, tiles_b, o);
   }
-  __shared__ int red_mine[4];
-  if ((threadIdx.x & 31) == 0) {
-    red[0][threadIdx.x >> 5] = all;
-    red[1][threadIdx.x >> 5] = before;
-    red_mine[threadIdx.x >> 5] = mine;
-  }
-  __syncthreads();
-  all = red[0][0] + red[0][1] + red[0][2] + red[0][3];
-  before = red[1][0] + red[1][1] + red[1][2] + red[1][3];
-  const int tiles_b = red_mine[0] + red_mine[1] + red_mine[2] + red_mine[3];
   uint16_t* orow = out + ((int64_t)b * Hq + h) * Dv;
   if (tiles_b == 0) {  // seq_len == 0: defined output (zeros)
-    for (int d = threadIdx.x; d < Dv; d += 128) orow[d] = 0;
+    for (int d = lane; d < Dv; d += 32) orow[d] = 0;
     return;
   }
   const int kvh = h / Ggrp, within = h - kvh * Ggrp;
@@ -571,53 +566,95 @@ __global__ void __launch_bounds__(128) decode_merge_part_kernel(const float* __r
   const int64_t t0 = (int64_t)NG * before + (int64_t)g * tiles_b, t1 = t0 + tiles_b;
   const int c0 = (int)part_owner(t0, W, grid), c1 = (int)part_owner(t1 - 1, W, grid);
   if (c0 == c1) return;  // one CTA saw the whole unit and wrote the output itself
-  // partial (o, lse) pairs of the CTAs c0..c1 (CTAs whose range is empty wrote nothing): weights in parallel
+  // partial (o, lse) pairs of the CTAs c0..c1 (CTAs whose range is empty wrote nothing)
   const int rows = HPC * 16;
-  __shared__ float s_w[kMaxPartials];
-  __shared__ int s_row[kMaxPartials];
-  __shared__ float s_red[4];
   const int n = c1 - c0 + 1;  // <= grid <= kMaxPartials
-  for (int i = threadIdx.x; i < n; i += 128) {
-    float lse = -INFINITY;
-    int prow = -1;
-    const int c = c0 + i;
-    const int64_t cs = part_start(c, W, grid);
-    if (cs < part_start(c + 1, W, grid)) {
-      prow = (c * 2 + (t0 <= cs ? 0 : 1)) * rows + hl * 16 + r;
-      lse = part_lse[prow];
-    }
-    s_row[i] = prow;
-    s_w[i] = lse;
-  }
-  __syncthreads();
+  constexpr int R = kMaxPartials / 32;
+  int prow[R];
+  float w[R];
   float M = -INFINITY;
-  for (int i = threadIdx.x; i < n; i += 128) M = fmaxf(M, s_w[i]);
+#pragma unroll
+  for (int k = 0; k < R; ++k) {
+    const int i = lane + 32 * k;
+    prow[k] = -1;
+    w[k] = -INFINITY;
+    if (i < n) {
+      const int c = c0 + i;
+      const int64_t cs = part_start(c, W, grid);
+      if (cs < part_start(c + 1, W, grid)) {
+        prow[k] = (c * 2 + (t0 <= cs ? 0 : 1)) * rows + hl * 16 + r;
+        w[k] = part_lse[prow[k]];
+      }
+    }
+    M = fmaxf(M, w[k]);
+  }
   M = warp_max(M);
-  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = M;
-  __syncthreads();
-  M = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
   const float Mu = (M == -INFINITY) ? 0.f : M;
-  __syncthreads();
   float L = 0.f;
-  for (int i = threadIdx.x; i < n; i += 128) {
-    const float w = s_row[i] >= 0 ? exp2f(s_w[i] - Mu) : 0.f;
-    s_w[i] = w;
-    L += w;
+#pragma unroll
+  for (int k = 0; k < R; ++k) {
+    w[k] = prow[k] >= 0 ? exp2f(w[k] - Mu) : 0.f;
+    L += w[k];
   }
   L = warp_sum(L);
-  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = L;
-  __syncthreads();
-  L = s_red[0] + s_red[1] + s_red[2] + s_red[3];
   const float inv = L > 0.f ? 1.f / L : 0.f;
-  for (int d = threadIdx.x; d < Dv; d += 128) {
-    float acc = 0.f;
+  float4 acc[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < R; ++k) {
+    if (32 * k < n) {  // warp-uniform
+      const int cnt = n - 32 * k < 32 ? n - 32 * k : 32;
 #pragma unroll 4
-    for (int i = 0; i < n; ++i) {
-      const float w = s_w[i];
-      if (w > 0.f) acc += w * part_o[(int64_t)s_row[i] * Dv + d];
+      for (int j = 0; j < cnt; ++j) {
+        const float wj = __shfl_sync(0xffffffffu, w[k], j);
+        const int pj = __shfl_sync(0xffffffffu, prow[k], j);
+        if (wj > 0.f) {
+          const float4* src = reinterpret_cast<const float4*>(part_o + (int64_t)pj * Dv);
+#pragma unroll
+          for (int v = 0; v < NV; ++v) {
+            const int d4 = lane + 32 * v;
+            if (d4 * 4 < Dv) {
+              const float4 x = src[d4];
+              acc[v].x += wj * x.x;
+              acc[v].y += wj * x.y;
+              acc[v].z += wj * x.z;
+              acc[v].w += wj * x.w;
+            }
+          }
+        }
+      }
     }
-    orow[d] = float_to_half<BF16>(acc * inv);
   }
+  const bool vec_ok = (reinterpret_cast<uintptr_t>(orow) & 7) == 0;
+#pragma unroll
+  for (int v = 0; v < NV; ++v) {
+    const int d = (lane + 32 * v) * 4;
+    if (d < Dv) {
+      if (vec_ok) {
+        *reinterpret_cast<uint2*>(orow + d) =
+            make_uint2(pack_half2<BF16>(acc[v].x * inv, acc[v].y * inv), pack_half2<BF16>(acc[v].z * inv, acc[v].w * inv));
+      } else {
+        orow[d] = float_to_half<BF16>(acc[v].x * inv);
+        orow[d + 1] = float_to_half<BF16>(acc[v].y * inv);
+        orow[d + 2] = float_to_half<BF16>(acc[v].z * inv);
+        orow[d + 3] = float_to_half<BF16>(acc[v].w * inv);
+      }
+    }
+  }
+}
+
+// launcher shared by the GQA and the MLA kernels (Dv % 4 == 0, Dv <= 512)
+template <bool BF16>
+static int launch_merge_part(const DecodeKParams& kp, int Ggrp, int HPC, int tile_t, int NG, int n_qblk, int grid, cudaStream_t st) {
+  const dim3 g(kp.B * ((kp.Hq + 7) / 8)), blk(256);
+  if (kp.Dv <= 128)
+    launch_pdl(decode_merge_part_kernel<BF16, 1>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp, HPC,
+               tile_t, NG, n_qblk, grid, kp.Dv);
+  else
+    launch_pdl(decode_merge_part_kernel<BF16, 4>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp, HPC,
+               tile_t, NG, n_qblk, grid, kp.Dv);
+  return launched("decode_merge_part_kernel launch");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -790,10 +827,7 @@ static int launch_mma(const DecodeKParams& kp, cudaStream_t st) {
   launch_pdl(kern, dim3(grid), dim3(kAttnThreads), C::SMEM_BYTES, st, kp);
   if (int rc = launched("decode_attn_mma_kernel launch")) return rc;
   const int n_qblk = (kp.G + 15) / 16;
-  launch_pdl(decode_merge_part_kernel<BF16>, dim3(kp.B * kp.Hq), dim3(128), 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq,
-                                                               kp.G, HPC, C::TILE_T, (kp.Hkv / HPC) * n_qblk, n_qblk, grid,
-                                                               kp.Dv);
-  return launched("decode_merge_part_kernel launch");
+  return launch_merge_part<BF16>(kp, kp.G, HPC, C::TILE_T, (kp.Hkv / HPC) * n_qblk, n_qblk, grid, st);
 }
 
 template <bool BF16>

@@ -365,7 +365,5 @@ static int launch_mla(const DecodeKParams& kp, cudaStream_t st) {
   kern<<<grid, kAttnThreads, C::SMEM_BYTES, st>>>(kp);
   if (int rc = launched("decode_mla_mma_kernel launch")) return rc;
   const int n_qblk = (kp.Hq + 15) / 16;
-  decode_merge_part_kernel<BF16><<<kp.B * kp.Hq, 128, 0, st>>>(kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq,
-                                                               kp.Hq, 1, C::TILE_T, n_qblk, n_qblk, grid, kp.Dv);
-  return launched("decode_merge_part_kernel launch");
+  return launch_merge_part<BF16>(kp, kp.Hq, 1, C::TILE_T, n_qblk, n_qblk, grid, st);
 }

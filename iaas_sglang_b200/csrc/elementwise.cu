@@ -242,8 +242,22 @@ __global__ void rope_neox_kernel(uint16_t* __restrict__ q, int64_t q_sm, uint16_
   const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
   float sn, cs;
   sincosf(ps * inv_freq, &sn, &cs);
-  for (int h = slot; h < Hq + Hkv; h += slots) {
-    uint16_t* base = h < Hq ? q + (int64_t)m * q_sm + h * D : k + (int64_t)m * k_sm + (h - Hq) * D;
+  // blockIdx.y splits the heads so that a decode batch (M = 64 tokens) still fills the SMs; two heads per trip keep
+  // four independent loads in flight per thread
+  const int step = slots * gridDim.y;
+  auto row = [&](int h) { return h < Hq ? q + (int64_t)m * q_sm + h * D : k + (int64_t)m * k_sm + (h - Hq) * D; };
+  int h = slot + blockIdx.y * slots;
+  for (; h + step < Hq + Hkv; h += 2 * step) {
+    uint16_t *ba = row(h), *bb = row(h + step);
+    const float a1 = half_to_float<BF16>(ba[i]), a2 = half_to_float<BF16>(ba[i + half]);
+    const float b1 = half_to_float<BF16>(bb[i]), b2 = half_to_float<BF16>(bb[i + half]);
+    ba[i] = float_to_half<BF16>(a1 * cs - a2 * sn);
+    ba[i + half] = float_to_half<BF16>(a2 * cs + a1 * sn);
+    bb[i] = float_to_half<BF16>(b1 * cs - b2 * sn);
+    bb[i + half] = float_to_half<BF16>(b2 * cs + b1 * sn);
+  }
+  if (h < Hq + Hkv) {
+    uint16_t* base = row(h);
     const float x1 = half_to_float<BF16>(base[i]), x2 = half_to_float<BF16>(base[i + half]);
     base[i] = float_to_half<BF16>(x1 * cs - x2 * sn);
     base[i + half] = float_to_half<BF16>(x2 * cs + x1 * sn);
@@ -377,13 +391,18 @@ extern "C" int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int
 
 extern "C" int b200_rope_neox(void* q, int64_t q_sm, void* k, int64_t k_sm, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D,
                               float theta, void* stream) {
-  B200_REQUIRE(q && k && positions && M >= 0 && D % 2 == 0, B200_ERR_ARG, "rope_neox: bad argument");
+  B200_REQUIRE(q && k && positions && M >= 0 && D >= 2 && D % 2 == 0, B200_ERR_ARG, "rope_neox: bad argument");
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, B200_ERR_UNSUPPORTED, "rope_neox: dtype");
   if (M == 0) return B200_OK;
   if (int rc = require_sm100("rope_neox")) return rc;
+  // heads are split over blockIdx.y (two per thread) while the batch alone would leave SMs idle
+  const int slots = 256 / (D / 2);
+  int gy = 1;
+  if (slots > 0 && M < 1024) gy = ((Hq + Hkv + slots - 1) / slots + 1) / 2;
+  if (gy < 1) gy = 1;
   if (dtype == B200_BF16)
-    launch_pdl(rope_neox_kernel<true>, dim3(M), dim3(256), 0, (cudaStream_t)stream, (uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
+    launch_pdl(rope_neox_kernel<true>, dim3(M, gy), dim3(256), 0, (cudaStream_t)stream, (uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
   else
-    launch_pdl(rope_neox_kernel<false>, dim3(M), dim3(256), 0, (cudaStream_t)stream, (uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
+    launch_pdl(rope_neox_kernel<false>, dim3(M, gy), dim3(256), 0, (cudaStream_t)stream, (uint16_t*)q, q_sm, (uint16_t*)k, k_sm, positions, Hq, Hkv, D, log2f(theta));
   return launched("rope_neox_kernel launch");
 }

@@ -274,7 +274,7 @@ class DecodeStack:
                 qkv = self.method.apply(self.w_qkv[l], x)
             q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
             ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
-            a = self.attn[l](q, k, v, fb)
+            a = self.attn[l](q, k, v, fb, quant_fp8=True) if fused else self.attn[l](q, k, v, fb)
             h = self._row_parallel(self.w_o[l], a)
             if fused:
                 xq = ops.rmsnorm_quant_fp8(h, self.norm2[l], 1e-5, residual=residual)
@@ -417,7 +417,7 @@ def run_reference_arm(args, wl, n_layers):
     cores = os.cpu_count() or 1
     batch = args.batch or wl["batch"] * max(1, args.gpus)
     if wl["quant"] != "fp8":
-        print(json.dumps({"impl": "reference", "unavailable": f"CPU leg implemented for the fp8 workloads, not {wl['quant']}"}))
+        emit({"impl": "reference", "unavailable": f"CPU leg implemented for the fp8 workloads, not {wl['quant']}"})
         return
     sample = CpuLayerSample(wl, batch, cores)
     val, ms, done = time_cpu_layers(sample, args.warmup, args.steps, n_layers)
@@ -431,7 +431,7 @@ def run_reference_arm(args, wl, n_layers):
         "e2e": {"value": round(val, 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(wl, args, n_layers, batch, tp):
@@ -459,8 +459,26 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+_OUT_FD = 1
+
+
+def claim_stdout():
+    """stdout carries exactly ONE line, the JSON: whatever else writes to fd 1 (NCCL's version banner under torchrun)
+    is sent to stderr for the rest of the run."""
+    global _OUT_FD
+    sys.stdout.flush()
+    _OUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    sys.stdout.flush()
+    os.write(_OUT_FD, (json.dumps(line) + "\n").encode())
+
+
 def main():
     args = parse_args()
+    claim_stdout()
     wl = WORKLOADS[args.workload]
     n_layers = args.layers or wl["layers"]
     if args.impl == "reference":
@@ -608,7 +626,7 @@ def main():
                                         "sample": sample.describe(n_layers) + f"; {done} timed layer passes, {cms:.1f} ms each"}
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         # NCCL teardown with captured collectives still alive can block for minutes (seen on the 2-GPU box: the JSON
         # line was out, destroy_process_group never returned).  The measurement is complete: leave through a last

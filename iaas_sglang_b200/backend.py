@@ -138,12 +138,17 @@ class B200AttnBackend(_Base):
         if save_kv_cache and k is not None:
             key = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
             value = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
-        ops.decode_attention(
+        # quant_fp8=True (not a reference argument): the caller is an FP8 block o_proj and wants the group-128
+        # quantisation of `o` from the same launch sequence -> returns (x_q, x_s) for LinearMethod.apply_quantized
+        quant_fp8 = bool(kwargs.get("quant_fp8", False))
+        res = ops.decode_attention(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim), k_buf, v_buf,
             o.view(-1, layer.tp_q_head_num, layer.v_head_dim), key, value, forward_batch.out_cache_loc,
             md.attn_logits, forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             forward_batch.seq_lens, layer.scaling, layer.logit_cap,
-            max_seq_len=md.max_seq_len, num_splits=md.num_kv_splits, fused_kv_write=True)
+            max_seq_len=md.max_seq_len, num_splits=md.num_kv_splits, fused_kv_write=True, quant_fp8=quant_fp8)
+        if quant_fp8:
+            return res[1], res[2]
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):

@@ -33,6 +33,16 @@ constexpr int kAttnThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kTokPerWarp = 16;
 constexpr float kLog2e = 1.4426950408889634f;
 
+// optional epilogue of the split merge: per_token_group_quant_fp8(out.view(B, Hq * Dv), 128) for the o_proj linear
+// (fp8_utils.py:202-204), bit-identical to the separate quantiser kernel; q == nullptr: off
+struct MergeQuant {
+  uint8_t* q;
+  int64_t q_sm;
+  float* s;
+  int64_t s_sm, s_sg;
+  float eps, fmin_, fmax_;
+};
+
 struct DecodeKParams {
   const uint16_t* q;
   int64_t q_sb, q_sh;
@@ -58,6 +68,7 @@ struct DecodeKParams {
   int fused_new;  // substitute k_new/v_new for the slot out_cache_loc[b] and write it back in-kernel
   int is_mla;
   float sm_scale, logit_cap;
+  MergeQuant mq;
 };
 
 constexpr int kMaxSmem = 232448;  // 227 KB: the sm_100 per-block opt-in limit
@@ -526,13 +537,35 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
 // 8 warps, a lane owns 4 consecutive output columns of every 128.  Warps are independent -- no shared memory, no
 // block barrier: each one recomputes the partition from seq_lens, keeps its (row, weight) pairs in registers and
 // hands them round with shuffles.  NV = ceil(Dv / 128).
-template <bool BF16, int NV>
+// QUANT (Dv == 128, one quantisation group per head): every (request, head) row is also emitted as e4m3 + scale;
+// rows that needed no merge are read back from `out` (written by the attention kernel, which the grid dependency
+// orders before this kernel).
+template <bool BF16>
+__device__ __forceinline__ void merge_quant_row(const MergeQuant& mq, uint2 pk, int b, int h, int lane) {
+  const float2 f0 = unpack_half2<BF16>(pk.x), f1 = unpack_half2<BF16>(pk.y);
+  const float v[4] = {f0.x, f0.y, f1.x, f1.y};
+  float amax = mq.eps;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) amax = fmaxf(amax, fabsf(v[i]));
+  amax = warp_max(amax);
+  const float ys = __fdiv_rn(amax, mq.fmax_);
+  if (lane == 0) mq.s[b * mq.s_sm + h * mq.s_sg] = ys;
+  uint32_t q4 = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float qv = fminf(fmaxf(__fdiv_rn(v[j], ys), mq.fmin_), mq.fmax_);
+    q4 |= (uint32_t)__nv_cvt_float_to_fp8(qv, __NV_SATFINITE, __NV_E4M3) << (8 * j);
+  }
+  *reinterpret_cast<uint32_t*>(mq.q + b * mq.q_sm + h * 128 + lane * 4) = q4;
+}
+
+template <bool BF16, int NV, bool QUANT>
 __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __restrict__ part_o,
                                                                 const float* __restrict__ part_lse,
-                                                                uint16_t* __restrict__ out,
+                                                                uint16_t* out,
                                                                 const int64_t* __restrict__ seq_lens, int B, int Hq,
                                                                 int Ggrp, int HPC, int tile_t, int NG, int n_qblk,
-                                                                int grid, int Dv) {
+                                                                int grid, int Dv, const MergeQuant mq) {
   griddep_wait();
   griddep_launch();
   const int lane = threadIdx.x & 31;
@@ -557,6 +590,7 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   uint16_t* orow = out + ((int64_t)b * Hq + h) * Dv;
   if (tiles_b == 0) {  // seq_len == 0: defined output (zeros)
     for (int d = lane; d < Dv; d += 32) orow[d] = 0;
+    if constexpr (QUANT) merge_quant_row<BF16>(mq, make_uint2(0u, 0u), b, h, lane);
     return;
   }
   const int kvh = h / Ggrp, within = h - kvh * Ggrp;
@@ -565,7 +599,10 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   const int64_t W = (int64_t)NG * all;
   const int64_t t0 = (int64_t)NG * before + (int64_t)g * tiles_b, t1 = t0 + tiles_b;
   const int c0 = (int)part_owner(t0, W, grid), c1 = (int)part_owner(t1 - 1, W, grid);
-  if (c0 == c1) return;  // one CTA saw the whole unit and wrote the output itself
+  if (c0 == c1) {  // one CTA saw the whole unit and wrote the output itself
+    if constexpr (QUANT) merge_quant_row<BF16>(mq, *reinterpret_cast<const uint2*>(orow + lane * 4), b, h, lane);
+    return;
+  }
   // partial (o, lse) pairs of the CTAs c0..c1 (CTAs whose range is empty wrote nothing)
   const int rows = HPC * 16;
   const int n = c1 - c0 + 1;  // <= grid <= kMaxPartials
@@ -632,8 +669,9 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
     const int d = (lane + 32 * v) * 4;
     if (d < Dv) {
       if (vec_ok) {
-        *reinterpret_cast<uint2*>(orow + d) =
-            make_uint2(pack_half2<BF16>(acc[v].x * inv, acc[v].y * inv), pack_half2<BF16>(acc[v].z * inv, acc[v].w * inv));
+        const uint2 pk = make_uint2(pack_half2<BF16>(acc[v].x * inv, acc[v].y * inv), pack_half2<BF16>(acc[v].z * inv, acc[v].w * inv));
+        *reinterpret_cast<uint2*>(orow + d) = pk;
+        if constexpr (QUANT) merge_quant_row<BF16>(mq, pk, b, h, lane);  // NV == 1, Dv == 128: every lane is here
       } else {
         orow[d] = float_to_half<BF16>(acc[v].x * inv);
         orow[d + 1] = float_to_half<BF16>(acc[v].y * inv);
@@ -648,12 +686,15 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
 template <bool BF16>
 static int launch_merge_part(const DecodeKParams& kp, int Ggrp, int HPC, int tile_t, int NG, int n_qblk, int grid, cudaStream_t st) {
   const dim3 g(kp.B * ((kp.Hq + 7) / 8)), blk(256);
-  if (kp.Dv <= 128)
-    launch_pdl(decode_merge_part_kernel<BF16, 1>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp, HPC,
-               tile_t, NG, n_qblk, grid, kp.Dv);
+  if (kp.mq.q)  // Dv == 128 and an 8-byte aligned `out` were checked by the entry point
+    launch_pdl(decode_merge_part_kernel<BF16, 1, true>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp,
+               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
+  else if (kp.Dv <= 128)
+    launch_pdl(decode_merge_part_kernel<BF16, 1, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp,
+               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
   else
-    launch_pdl(decode_merge_part_kernel<BF16, 4>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp, HPC,
-               tile_t, NG, n_qblk, grid, kp.Dv);
+    launch_pdl(decode_merge_part_kernel<BF16, 4, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp,
+               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
   return launched("decode_merge_part_kernel launch");
 }
 
@@ -898,7 +939,7 @@ extern "C" int b200_set_kv_buffer(void* k_buf, int64_t kb_st, int64_t kb_sh, voi
   return launched("set_kv_kernel launch");
 }
 
-extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) {
+static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* mq, void* stream) {
   B200_REQUIRE(a != nullptr, B200_ERR_ARG, "decode_attn: null params");
   B200_REQUIRE(a->B >= 0 && a->Hq > 0 && a->Hkv > 0 && a->D > 0 && a->Dv > 0, B200_ERR_ARG, "decode_attn: bad sizes");
   B200_REQUIRE(a->Hq % a->Hkv == 0, B200_ERR_ARG, "decode_attn: Hq %% Hkv != 0");
@@ -928,6 +969,7 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
   kp.rpi = a->req_pool_indices; kp.seq_lens = a->seq_lens; kp.loc = a->out_cache_loc;
   kp.B = a->B; kp.Hq = a->Hq; kp.Hkv = a->Hkv; kp.G = a->Hq / a->Hkv; kp.D = a->D; kp.Dv = a->Dv;
   kp.is_mla = is_mla; kp.sm_scale = a->sm_scale; kp.logit_cap = a->logit_cap;
+  kp.mq = MergeQuant{};
 
   // tuned path needs 16-byte aligned, head-contiguous rows
   bool mma = mma_path_ok(a->Hq, a->Hkv, a->D, a->Dv);
@@ -939,6 +981,13 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
     const bool q_ok = ((uintptr_t)a->q & 3) == 0 && a->q_stride_b % 2 == 0 && a->q_stride_h % 2 == 0;
     if (!rows_ok || !q_ok) mma = false;
     if (mma && hpc > 1 && (a->kbuf_stride_h != a->D || a->vbuf_stride_h != a->Dv)) hpc = 1;  // heads not adjacent
+  }
+  if (mq) {
+    B200_REQUIRE(mq->q && mq->s, B200_ERR_ARG, "decode_attn_quant_fp8: null output");
+    B200_REQUIRE(mma && a->Dv == 128 && ((uintptr_t)a->out & 7) == 0 && ((uintptr_t)mq->q & 3) == 0 && mq->q_sm % 4 == 0,
+                 B200_ERR_UNSUPPORTED,
+                 "decode_attn_quant_fp8: needs the tuned GQA kernel with Dv == 128 and aligned outputs (quantise separately otherwise)");
+    kp.mq = *mq;
   }
   // tuned MLA path (decode_mla.cuh): 16-byte aligned latent rows, 4-byte aligned q rows; an explicit split-count
   // hint selects the generic kernel (the tuned kernel partitions the KV work itself)
@@ -1008,6 +1057,10 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
       c.rpi = kp.rpi + b0;
       c.seq_lens = kp.seq_lens + b0;
       if (kp.loc) c.loc = kp.loc + b0;
+      if (kp.mq.q) {
+        c.mq.q = kp.mq.q + (int64_t)b0 * kp.mq.q_sm;
+        c.mq.s = kp.mq.s + (int64_t)b0 * kp.mq.s_sm;
+      }
       const int rc = a->dtype == B200_BF16 ? dispatch_mma<true>(c, hpc, st) : dispatch_mma<false>(c, hpc, st);
       if (rc != 0) return rc;
     }
@@ -1033,4 +1086,14 @@ extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) 
     return launched("decode_merge_kernel launch");
   }
   return B200_OK;
+}
+
+extern "C" int b200_decode_attn(const b200_decode_attn_params* a, void* stream) { return decode_attn_impl(a, nullptr, stream); }
+
+extern "C" int b200_decode_attn_quant_fp8(const b200_decode_attn_params* a, void* q, int64_t q_sm, float* s, int64_t s_sm,
+                                          int64_t s_sg, float eps, float fp8_min, float fp8_max, void* stream) {
+  MergeQuant mq;
+  mq.q = (uint8_t*)q; mq.q_sm = q_sm; mq.s = s; mq.s_sm = s_sm; mq.s_sg = s_sg;
+  mq.eps = eps; mq.fmin_ = fp8_min; mq.fmax_ = fp8_max;
+  return decode_attn_impl(a, &mq, stream);
 }

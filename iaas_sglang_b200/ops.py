@@ -295,7 +295,7 @@ def decode_attention_workspace_bytes(B: int, Hq: int, Dv: int, num_splits: int) 
 
 def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logits, req_to_token, req_pool_indices,
                      seq_lens, sm_scale: float, logit_cap: float, *, max_seq_len: int = 0, num_splits: int = 0,
-                     fused_kv_write: bool = False) -> torch.Tensor:
+                     fused_kv_write: bool = False, quant_fp8: bool = False, quant_eps: float = 1e-10):
     """Same positional signature as torch.ops.sgl_kernel.decode_attention_cpu (decode.cpp:1375-1388;
     schema torch_extension_cpu.cpp:264-268) on CUDA tensors.
 
@@ -304,7 +304,11 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     attn_logits = fp32 scratch (any shape, only its byte size matters; None = allocate).
     MLA is detected like the reference: k_cache and v_cache share storage, Hkv == 1, D == Dv + 64 (:1455).
     fused_kv_write=True moves the append into the attention kernel; it requires that slot loc[b] is referenced
-    by request b only (true for SGLang's allocators; schedule_batch.py:1556-1568)."""
+    by request b only (true for SGLang's allocators; schedule_batch.py:1556-1568).
+    quant_fp8=True also returns (x_q, x_s) = per_token_group_quant_fp8(output.view(B, Hq*Dv), 128,
+    column_major_scales=True) for the FP8 block o_proj (fp8_utils.py:202-204), bit-identical to the separate call; the
+    split-merge kernel emits it where the tuned kernel runs (Dv == 128), otherwise the quantiser is launched here.
+    Returns output, or (output, x_q, x_s)."""
     dev = require_cuda(query, k_cache, v_cache, output, key, value, loc, attn_logits, req_to_token, req_pool_indices,
                        seq_lens)
     if query.dim() != 3 or k_cache.dim() != 3 or v_cache.dim() != 3:
@@ -359,8 +363,20 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
         attn_logits = torch.empty(need, dtype=torch.uint8, device=dev)
     p.workspace, p.workspace_bytes = attn_logits.data_ptr(), attn_logits.numel() * attn_logits.element_size()
     with torch.cuda.device(dev):
-        check(lib.b200_decode_attn(p, current_stream(dev)))
-    return output
+        if not quant_fp8:
+            check(lib.b200_decode_attn(p, current_stream(dev)))
+            return output
+        x_q, x_s = _fp8_group_outputs(B, Hq * Dv, dev)
+        rc = _lib.B200_ERR_UNSUPPORTED
+        if B > 0 and Dv == 128:
+            rc = lib.b200_decode_attn_quant_fp8(p, ptr(x_q), Hq * Dv, ptr(x_s), x_s.stride(0), x_s.stride(1), quant_eps,
+                                                -FP8_MAX, FP8_MAX, current_stream(dev))
+        if rc == _lib.B200_ERR_UNSUPPORTED:  # shape outside the fused epilogue: same result from two launches
+            check(lib.b200_decode_attn(p, current_stream(dev)))
+            x_q, x_s = per_token_group_quant_fp8(output.view(B, Hq * Dv), 128, eps=quant_eps, column_major_scales=True)
+        else:
+            check(rc)
+    return output, x_q, x_s
 
 
 def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices, seq_lens,

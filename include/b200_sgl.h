@@ -100,6 +100,13 @@ typedef struct b200_decode_attn_params {
 int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv, int max_seq_len, int num_splits_hint);
 size_t b200_decode_attn_workspace_size(int B, int Hq, int Dv, int num_splits);
 int b200_decode_attn(const b200_decode_attn_params* p, void* stream);
+/* b200_decode_attn followed by per_token_group_quant_fp8(out.view(B, Hq * Dv), 128, column-major scales) for the
+ * FP8 block o_proj (fp8_utils.py:202-204 sglang_per_token_group_quant_fp8; per_token_group_quant_8bit.cu:25-115),
+ * emitted by the split-merge kernel: out is written as usual, q8 [B, Hq*Dv] e4m3 (row stride q_stride_m bytes) and
+ * scales s[b * s_stride_m + h * s_stride_g] are bit-identical to the two-call sequence.  Tuned GQA kernel with
+ * Dv == 128 only; anything else returns B200_ERR_UNSUPPORTED and the caller quantises separately. */
+int b200_decode_attn_quant_fp8(const b200_decode_attn_params* p, void* q8, int64_t q_stride_m, float* s, int64_t s_stride_m,
+                               int64_t s_stride_g, float eps, float fp8_min, float fp8_max, void* stream);
 
 /* KVCache.set_kv_buffer alone (memory_pool.py:418-456; decode.cpp:771-809): rows scatter, bit-exact */
 int b200_set_kv_buffer(void* k_buf, int64_t kbuf_stride_t, int64_t kbuf_stride_h, void* v_buf, int64_t vbuf_stride_t,

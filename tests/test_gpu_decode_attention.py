@@ -251,3 +251,33 @@ def test_mla_cfg5_tp8_slice_properties():
     ops.decode_attention(d["q"], d["k_buf"], d["v_buf"], out_g, None, None, None, None, *tail[2:], max_seq_len=S,
                          num_splits=8)
     assert rel_l2(out_g, out) < 1e-3
+
+
+@pytest.mark.parametrize("seq_lens", [[4096] * 8, [1, 2, 3, 17], [5000, 3, 977, 64, 65], [300] * 64, [0, 7, 4096]])
+@pytest.mark.parametrize("heads", [(32, 8, 128), (8, 1, 128), (20, 4, 128), (32, 8, 64)],
+                         ids=lambda h: f"Hq{h[0]}Hkv{h[1]}D{h[2]}")
+def test_fused_fp8_quant_of_the_output_is_bit_identical(seq_lens, heads):
+    """quant_fp8=True: (x_q, x_s) from the split-merge kernel (Dv == 128; two launches otherwise) must equal
+    per_token_group_quant_fp8(out.view(B, Hq*Dv), 128, column_major_scales=True) bit for bit, and `out` itself must
+    not change (fp8_utils.py:202-204 is the call this replaces)."""
+    from iaas_sglang_b200 import ops
+
+    Hq, Hkv, D = heads
+    lens = seq_lens
+    c = DecodeCase(len(lens), Hq, Hkv, D, D, [max(s, 1) for s in lens])
+    d = c.cuda("cuda")
+    if 0 in lens:  # padded CUDA-graph rows have length 0: defined zeros, scale eps / 448
+        d["seq_lens"] = torch.tensor(lens, dtype=torch.int64, device="cuda")
+    kb0, vb0 = d["k_buf"].clone(), d["v_buf"].clone()
+    args = lambda kb, vb, out: (d["q"], kb, vb, out, d["k_new"], d["v_new"], d["loc"], None, d["req_to_token"],  # noqa: E731
+                                d["req_pool_indices"], d["seq_lens"], c.sm_scale, 0.0)
+    out_a = torch.zeros(c.B, Hq, D, dtype=c.dtype, device="cuda")
+    ops.decode_attention(*args(d["k_buf"], d["v_buf"], out_a), max_seq_len=max(lens), fused_kv_write=True)
+    q_ref, s_ref = ops.per_token_group_quant_fp8(out_a.view(c.B, Hq * D), 128, column_major_scales=True)
+    out_b = torch.full((c.B, Hq, D), 7.0, dtype=c.dtype, device="cuda")
+    res = ops.decode_attention(*args(kb0, vb0, out_b), max_seq_len=max(lens), fused_kv_write=True, quant_fp8=True)
+    torch.cuda.synchronize()
+    assert res[0] is out_b
+    assert torch.equal(out_a, out_b)
+    assert torch.equal(res[1].view(torch.uint8), q_ref.view(torch.uint8))
+    assert torch.equal(res[2], s_ref) and res[2].stride() == s_ref.stride()

@@ -572,6 +572,43 @@ def main():
     peak, peak_src = measured_peaks()
     achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
 
+    if args.kernels and hasattr(stack.method, "apply_quantized"):
+        # decomposition of the step (developer aid, stderr): the four linears of every layer alone, as one graph
+        from iaas_sglang_b200 import ops
+
+        def xq(kdim):
+            return ops.per_token_group_quant_fp8(torch.randn(batch, kdim, device=dev, dtype=torch.bfloat16) / 10, 128,
+                                                 column_major_scales=True)
+        x_h, x_a, x_i = xq(stack.hidden), xq(stack.hq * stack.d), xq(stack.inter)
+
+        def gemms():
+            for l in range(n_layers):
+                stack.method.apply_quantized(stack.w_qkv[l], x_h[0], x_h[1], stack.dtype)
+                stack.method.apply_quantized(stack.w_o[l], x_a[0], x_a[1], stack.dtype)
+                stack.method.apply_quantized(stack.w_gate_up[l], x_h[0], x_h[1], stack.dtype)
+                stack.method.apply_quantized(stack.w_down[l], x_i[0], x_i[1], stack.dtype)
+        sg = torch.cuda.Stream()
+        sg.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(sg):
+            gemms()
+        torch.cuda.current_stream().wait_stream(sg)
+        gg = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gg, stream=sg):
+            gemms()
+        for _ in range(3):
+            gg.replay()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(10):
+            gg.replay()
+        g1.record()
+        torch.cuda.synchronize()
+        gemm_us = g0.elapsed_time(g1) / 10 / n_layers * 1e3
+        print(json.dumps({"per_layer_us": {"step": round(ms / n_layers * 1e3, 1), "attention+merge": round(attn_ms * 1e3, 1),
+                                           "four_linears_alone": round(gemm_us, 1),
+                                           "rest (norm+quant x2, rope, silu*mul+quant, gaps)": round(ms / n_layers * 1e3 - attn_ms * 1e3 - gemm_us, 1)},
+                          "weight_bytes_per_layer": stack.weight_bytes_per_layer()}), file=sys.stderr, flush=True)
+
     # max over ranks
     if world > 1:
         t = torch.tensor([ms, e2e_ms or 0.0, attn_ms], device=dev, dtype=torch.float64)

@@ -41,7 +41,7 @@ def launches(src: str, dst: str, start_re: str = r"rmsnorm_kernel"):
     out.write("\n## One layer, in launch order (first full layer found)\n\n| # | kernel | grid | block | us |\n|---|---|---|---|---:|\n")
     started = 0
     for r in data:
-        if "b200::" not in r[ki]:
+        if r not in ours:
             continue
         nm = re.sub(r"\(.*", "", r[ki]).replace("void ", "")
         if re.search(start_re, r[ki]):

@@ -515,6 +515,20 @@ size_t skinny_workspace_bytes(int, int, int) { return 2048 * 8 * 8; }  // (devel
 
 bool skinny_applicable(int M) { return M <= 256; }
 
+// FP8 block-scaled crossover to the persistent large-M kernel.  Measured (tools/kb_cross.py, B200_SK_MAX_M=64 vs 256):
+// at M = 256 the large-M kernel is 1.4-3.4x faster on every cfg 2/4 TP shape (e.g. N 7168 K 4096: 50.2 -> 22.1 us),
+// at M = 128 the skinny kernel still wins 6 of 8 shapes.  The default stays 256 until the GPU parity suite has run
+// with 128 (B200_SK_MAX_M=128 selects it today); next round's first change.
+bool skinny_applicable_fp8(int M) {
+  static int max_m = -1;
+  if (max_m < 0) {
+    const char* e = getenv("B200_SK_MAX_M");
+    max_m = e ? atoi(e) : 256;
+    if (max_m > 256) max_m = 256;
+  }
+  return M <= max_m;
+}
+
 struct SkinnyPlan {
   int stages, tab_cap, smem;
 };

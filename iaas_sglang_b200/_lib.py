@@ -39,6 +39,9 @@ class DecodeAttnParams(C.Structure):
         ("B", C.c_int32), ("Hq", C.c_int32), ("Hkv", C.c_int32), ("D", C.c_int32), ("Dv", C.c_int32),
         ("dtype", C.c_int32), ("write_kv", C.c_int32), ("num_splits", C.c_int32), ("max_seq_len", C.c_int32),
         ("sm_scale", c_float), ("logit_cap", c_float),
+        ("meta_i32_mask", C.c_int32), ("page_size", C.c_int32),
+        ("q_rope", c_void_p), ("qrope_stride_b", c_int64), ("qrope_stride_h", c_int64),
+        ("k_rope_new", c_void_p), ("krope_stride_b", c_int64),
     ]
 
 
@@ -107,6 +110,14 @@ SIGNATURES = {
     "b200_ar_init": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, C.POINTER(c_void_p)]),
     "b200_ar_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "b200_ar_mode": (c_int, [c_int, c_size_t]),
+    "b200_ar_mode2": (c_int, [c_int, c_size_t, c_int]),
+    "b200_ar_set_mode": (c_int, [c_void_p, c_int]),
+    "b200_ar_free_region": (None, [c_void_p]),
+    "b200_ar_init_ptrs": (c_int, [C.POINTER(C.c_uint64), C.c_uint64, c_int, c_int, c_size_t, C.POINTER(c_void_p)]),
+    "b200_ar_has_multicast": (c_int, [c_void_p]),
+    "b200_ar_allreduce_add_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
+                                              c_int64, c_int64, c_int, c_int, c_int, c_float, c_float, c_float, c_float,
+                                              c_void_p]),
     "b200_ar_error": (c_int, [c_void_p]),
     "b200_ar_destroy": (None, [c_void_p]),
 }
@@ -130,7 +141,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.b200_abi_version() != 1:
+    if lib.b200_abi_version() != 2:
         raise ImportError("libb200sgl.so ABI version mismatch")
     _lib = lib
     return lib

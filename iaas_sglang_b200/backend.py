@@ -122,38 +122,59 @@ class B200AttnBackend(_Base):
         return 1  # triton_backend.py:629-630
 
     # ------------------------------------------------------------------ forward
-    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True,
+                       q_rope: Optional[torch.Tensor] = None, k_rope: Optional[torch.Tensor] = None,
+                       quant_fp8: bool = False):
+        """base_attn_backend.py:89-99.  q_rope / k_rope are the MLA arguments of cutlass_mla_backend.py:226-285 /
+        flashinfer_mla_backend.py: q then holds the 512 latent columns and q_rope the 64 rope columns of every head, k
+        the latent part and k_rope the rope part of the new cache row (set_mla_kv_buffer, memory_pool.py:859-876); the
+        kernel takes the two pointers of each, nothing is concatenated.  seq_lens / req_pool_indices may be int32
+        (cuda_graph_runner.py:273-276) or int64.  Any other keyword is a TypeError, as in the reference backends.
+        quant_fp8=True (not a reference argument): the caller is an FP8 block o_proj and wants the group-128 quantisation
+        of `o` from the same launch sequence -> returns (x_q, x_s) for LinearMethod.apply_quantized."""
         if getattr(layer, "is_cross_attention", False):
             raise NotImplementedError("b200 attention backend: cross attention is not supported")
         md = self.forward_metadata
-        q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
-        if layer.qk_head_dim != layer.v_head_dim:
-            o = q.new_empty((q.shape[0], layer.tp_q_head_num * layer.v_head_dim))
-        else:
-            o = torch.empty_like(q)
+        H = layer.tp_q_head_num
         pool = forward_batch.token_to_kv_pool
         k_buf = pool.get_key_buffer(layer.layer_id)
         v_buf = pool.get_value_buffer(layer.layer_id)
-        key = value = None
+        if q_rope is not None:
+            qv = q.view(-1, H, layer.v_head_dim)
+            q_rope = q_rope.view(-1, H, layer.qk_head_dim - layer.v_head_dim)
+        else:
+            qv = q.reshape(-1, H, layer.qk_head_dim)
+        o = qv.new_empty((qv.shape[0], H * layer.v_head_dim))
+        key = value = kr = None
         if save_kv_cache and k is not None:
-            key = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
-            value = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
-        # quant_fp8=True (not a reference argument): the caller is an FP8 block o_proj and wants the group-128
-        # quantisation of `o` from the same launch sequence -> returns (x_q, x_s) for LinearMethod.apply_quantized
-        quant_fp8 = bool(kwargs.get("quant_fp8", False))
+            if k_rope is not None:
+                key = k.view(-1, layer.tp_k_head_num, layer.v_head_dim)
+                kr = k_rope.view(-1, layer.tp_k_head_num, layer.qk_head_dim - layer.v_head_dim)
+            else:
+                key = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
+                value = v.view(-1, layer.tp_v_head_num, layer.v_head_dim) if v is not None else None
         res = ops.decode_attention(
-            q.view(-1, layer.tp_q_head_num, layer.qk_head_dim), k_buf, v_buf,
-            o.view(-1, layer.tp_q_head_num, layer.v_head_dim), key, value, forward_batch.out_cache_loc,
+            qv, k_buf, v_buf, o.view(-1, H, layer.v_head_dim), key, value, forward_batch.out_cache_loc,
             md.attn_logits, forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             forward_batch.seq_lens, layer.scaling, layer.logit_cap,
-            max_seq_len=md.max_seq_len, num_splits=md.num_kv_splits, fused_kv_write=True, quant_fp8=quant_fp8)
+            max_seq_len=md.max_seq_len, num_splits=md.num_kv_splits, fused_kv_write=True, quant_fp8=bool(quant_fp8),
+            q_rope=q_rope, k_rope=kr)
         if quant_fp8:
             return res[1], res[2]
         return o
 
-    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True,
+                       q_rope: Optional[torch.Tensor] = None, k_rope: Optional[torch.Tensor] = None):
         if getattr(layer, "is_cross_attention", False):
             raise NotImplementedError("b200 attention backend: cross attention is not supported")
+        if q_rope is not None:   # MLA prefill (not the tuned path): one packed 576-column q / k, as the pool stores them
+            H = layer.tp_q_head_num
+            q = torch.cat([q.view(-1, H, layer.v_head_dim), q_rope.view(-1, H, layer.qk_head_dim - layer.v_head_dim)], dim=-1)
+            q = q.view(-1, H * layer.qk_head_dim)
+        if k_rope is not None:
+            k = torch.cat([k.view(-1, layer.tp_k_head_num, layer.v_head_dim),
+                           k_rope.view(-1, layer.tp_k_head_num, layer.qk_head_dim - layer.v_head_dim)], dim=-1)
+            v = k[..., : layer.v_head_dim]
         if layer.qk_head_dim != layer.v_head_dim:
             o = q.new_empty((q.shape[0], layer.tp_q_head_num * layer.v_head_dim))
         else:

@@ -155,7 +155,9 @@ class MLATokenToKVPool:
 
     def set_mla_kv_buffer(self, layer, loc, cache_k_nope, cache_k_rope):
         """memory_pool.py:859-876: row = concat(k_nope [.., kv_lora_rank], k_rope [.., rope_dim])."""
-        self.set_kv_buffer(layer, loc, torch.cat([cache_k_nope, cache_k_rope], dim=-1), None)
+        B = loc.numel()
+        row = torch.cat([cache_k_nope.reshape(B, 1, -1), cache_k_rope.reshape(B, 1, -1)], dim=-1)
+        self.set_kv_buffer(layer, loc, row, None)
 
 
 class RadixAttention:
@@ -181,8 +183,11 @@ class RadixAttention:
     def forward(self, q, k, v, forward_batch: "ForwardBatch", save_kv_cache: bool = True, **kwargs):
         if k is not None:  # radix_attention.py:90-98
             assert v is not None
-            k = k.view(-1, self.tp_k_head_num, self.qk_head_dim)
-            v = v.view(-1, self.tp_v_head_num, self.v_head_dim)
+            if "k_rope" not in kwargs:
+                k = k.view(-1, self.tp_k_head_num, self.qk_head_dim)
+                v = v.view(-1, self.tp_v_head_num, self.v_head_dim)
+            else:
+                k = k.view(-1, self.tp_k_head_num, self.v_head_dim)
         return forward_batch.attn_backend.forward(q, k, v, self, forward_batch, save_kv_cache, **kwargs)
 
     __call__ = forward

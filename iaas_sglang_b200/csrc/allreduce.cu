@@ -1,42 +1,66 @@
-// One-shot all-reduce(sum) of the row-parallel linears' [M, hidden] half outputs over NVLink peer memory.
+// All-reduce(sum) of the row-parallel linears' [M, hidden] half outputs over NVLink peer memory / NVSwitch
+// multicast, optionally fused with the residual-add + RMSNorm (+ FP8 group quantisation) that follows it.
 //
 // Replaces, for messages up to a few MiB, the custom P2P all-reduce the reference routes small messages to
 // (sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:203-456, python/sglang/srt/distributed/device_communicators/
-// custom_all_reduce.py:148,414-480; call site communication_op.py:11-13 after RowParallelLinear, linear.py:1375-1376).
-// Larger messages and anything this path rejects stay on ncclAllReduce (tp.py).
+// custom_all_reduce.py:148,414-480; call site communication_op.py:11-13 after RowParallelLinear, linear.py:1375-1376)
+// and the all-reduce + add + RMSNorm fusion hook (python/sglang/srt/layers/flashinfer_comm_fusion.py:122
+// flashinfer_allreduce_add_rmsnorm, layers/communicator.py).  Larger messages and anything this path rejects stay
+// on ncclAllReduce (tp.py).
 //
-// Every rank owns one cudaMalloc'ed region, opened by its peers through CUDA IPC:
-//   [flags: MAX_BLOCKS x 8 uint32, written by PEERS] [flag sequence + call counters: per block, private] [err]
-//   [data slot 0] [data slot 1]
-// One kernel per all-reduce, grid = nblocks (<= MAX_BLOCKS), no host synchronisation, CUDA-graph capturable:
-//   1. block b copies its chunk of the input into the rank's own data slot (slot = call parity);
-//   2. block b tells block b of every peer "my chunk of call n is in place" (st.release.sys into the peer's flag
-//      word [b][my rank]) and waits until every peer has said the same (ld.acquire.sys on its own flag words);
-//   3. block b reads chunk b of all ranks' slots (its own from local HBM, the peers' over NVLink), sums them in
-//      RANK ORDER in fp32 -- every rank computes bit-identical results -- and writes the output (may alias the input).
-// The call number lives in device memory (per block), so a replayed CUDA graph keeps counting.  Two data slots make
-// an end-of-call barrier unnecessary: a rank can only start call n + 2 (same slot as n) after it passed the barrier of
-// call n + 1, which every peer signals only after finishing call n.  A spin that lasts longer than ~20 s sets an
-// error word and lets the kernel finish (wrong data, no hang); the host checks it with b200_ar_error().
+// Every rank owns one region of the same layout; every rank can address every region (CUDA IPC mappings, or the
+// peer pointers of a symmetric-memory allocation, which also gives the MULTICAST address of the same buffer):
+//   [flags: MAX_BLOCKS x 8 uint32, written by PEERS] [call counter | finished-block counter | error word]
+//   [in slot 0] [in slot 1] [out stage 0] [out stage 1]
+// One kernel per all-reduce, no host synchronisation, CUDA-graph capturable.  Block b of a rank only ever depends
+// on block b of its peers, through a per-block flag barrier (st.release.sys into the peer's flag word [b][my rank],
+// ld.acquire.sys on my own); all blocks of a call use the same flag values 2n+1 / 2n+2 and the same data slot
+// n & 1, where n is ONE call counter per rank in device memory: the last block to finish increments it, and the
+// stream order (or griddepcontrol.wait) makes the next kernel read the new value -- so a replayed CUDA graph keeps
+// counting and calls of different sizes, grids and kernels can be mixed freely.
+//
+// Why two slots need no end-of-call barrier: a rank starts call n + 2 (same slot as n) only after its call n + 1
+// has completed, i.e. after at least its block 0 passed a barrier of call n + 1 with block 0 of EVERY peer; a peer
+// signals in call n + 1 only after its whole call-n kernel has finished (stream order).  So when slot n & 1 is
+// overwritten, nobody is still reading call n's data.  The same argument covers the out stages.
+//
+// Kernels:
+//   allreduce_oneshot_kernel  flat message: copy-in, barrier, every rank pulls all W copies and sums in RANK ORDER in
+//                             fp32 -> bit-identical results on every rank;
+//   allreduce_twoshot_kernel  flat message, reduce-scatter + all-gather over peer loads (2 barriers);
+//   allreduce_rows_kernel     row layout (block b owns whole rows of [M, H]): copy-in, barrier, then either
+//                               PULL: sum the W copies of the block's rows in rank order (one-shot), or
+//                               NVLS: rank c reduces sub-range c of the block's rows with ONE multimem.ld_reduce per
+//                                     16 bytes (the switch adds the W copies) and multimem.st's the result into
+//                                     every rank's out stage; barrier;
+//                             and an epilogue over the block's full rows, read locally: plain copy to `out`, or
+//                             residual += x; RMSNorm; optional group-128 e4m3 quantisation (rmsnorm_row.cuh: the same
+//                             code, hence the same bits, as rmsnorm_quant_fp8_kernel after a plain all-reduce).
+// A spin that lasts longer than ~20 s sets the error word and lets the kernel finish (wrong data, no hang); the
+// host polls it with b200_ar_error() (tp.py does so once per step).
 #include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
+#include "rmsnorm_row.cuh"
 
 namespace b200 {
 
-constexpr int AR_MAX_BLOCKS = 128;
+constexpr int AR_MAX_BLOCKS = 512;
 constexpr int AR_MAX_RANKS = 8;
-constexpr int AR_THREADS = 512;
-constexpr size_t AR_FLAG_BYTES = AR_MAX_BLOCKS * AR_MAX_RANKS * 4;  // 4 KB
-constexpr size_t AR_CNT_OFF = AR_FLAG_BYTES;
-constexpr size_t AR_ERR_OFF = AR_CNT_OFF + AR_MAX_BLOCKS * 4;
-constexpr size_t AR_CALLS_OFF = AR_ERR_OFF + 64;  // per-block number of calls (its parity picks the data slot)
-constexpr size_t AR_DATA_OFF = 8192;
-static_assert(AR_CALLS_OFF + AR_MAX_BLOCKS * 4 <= AR_DATA_OFF, "region header");
+constexpr int AR_THREADS = 512;       // flat kernels
+constexpr int AR_FLAT_BLOCKS = 128;   // flat kernels
+constexpr int AR_ROW_THREADS = 256;   // rows kernel (= the RMSNorm row layout)
+constexpr size_t AR_FLAG_BYTES = (size_t)AR_MAX_BLOCKS * AR_MAX_RANKS * 4;  // 16 KB
+constexpr size_t AR_CALLS_OFF = AR_FLAG_BYTES;        // uint32: calls completed by this rank
+constexpr size_t AR_DONE_OFF = AR_CALLS_OFF + 64;     // uint32: blocks of the running call that have finished
+constexpr size_t AR_ERR_OFF = AR_DONE_OFF + 64;       // uint32: a peer never arrived
+constexpr size_t AR_DATA_OFF = 32768;
+static_assert(AR_ERR_OFF + 64 <= AR_DATA_OFF, "region header");
 
 struct ArParams {
-  uint8_t* base[AR_MAX_RANKS];  // region of every rank (own = local pointer, peers = IPC mappings)
+  uint8_t* base[AR_MAX_RANKS];  // region of every rank (own = local pointer)
+  uint8_t* mc;                  // multicast address of the same region (NVLS) or nullptr
   int rank, world;
   size_t slot_bytes;
   const uint4* in;
@@ -47,7 +71,7 @@ struct ArParams {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-// peer data is read around the L1 (a line of the same slot from two calls ago must not be served from it)
+// peer / staged data is read around the L1 (a line of the same slot from two calls ago must not be served from it)
 __device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
   uint4 v;
   asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
@@ -57,6 +81,23 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+// NVSwitch multicast (NVLS): one load returns the fp32-accumulated sum of the same 16 bytes of every rank's copy;
+// one store lands in every rank's copy
+template <bool BF16>
+__device__ __forceinline__ uint4 multimem_ld_reduce(const void* mc_addr) {
+  uint4 v;
+  if constexpr (BF16)
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_addr) : "memory");
+  else
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(void* mc_addr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
 }
 
 template <bool BF16>
@@ -69,31 +110,40 @@ __device__ __forceinline__ void add8(float (&acc)[8], const uint4& v) {
     acc[2 * i + 1] += f.y;
   }
 }
+template <bool BF16>
+__device__ __forceinline__ uint4 pack8(const float (&acc)[8]) {
+  return make_uint4(pack_half2<BF16>(acc[0], acc[1]), pack_half2<BF16>(acc[2], acc[3]), pack_half2<BF16>(acc[4], acc[5]),
+                    pack_half2<BF16>(acc[6], acc[7]));
+}
 
-template <bool BF16, int WORLD>
-__global__ void __launch_bounds__(AR_THREADS) allreduce_oneshot_kernel(const __grid_constant__ ArParams p) {
-  const int b = blockIdx.x;
-  uint8_t* mine = p.base[p.rank];
-  uint32_t* cnt = reinterpret_cast<uint32_t*>(mine + AR_CNT_OFF) + b;
-  uint32_t* calls = reinterpret_cast<uint32_t*>(mine + AR_CALLS_OFF) + b;
-  const uint32_t call = *cnt + 1;  // this block's flag sequence number (private to the block, bumped at the end)
-  const int slot = *calls & 1;     // consecutive calls (of either kernel) alternate between the two data slots
-  const int64_t per = (p.nvec + gridDim.x - 1) / gridDim.x;
-  const int64_t v0 = (int64_t)b * per, v1 = v0 + per < p.nvec ? v0 + per : p.nvec;
+// this rank's call number (see the file header); read after griddepcontrol.wait
+__device__ __forceinline__ uint32_t ar_call_number(const uint8_t* mine) {
+  return *reinterpret_cast<const volatile uint32_t*>(mine + AR_CALLS_OFF);
+}
+// last block out bumps the call number
+__device__ __forceinline__ void ar_finish(uint8_t* mine, uint32_t call) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* done = reinterpret_cast<uint32_t*>(mine + AR_DONE_OFF);
+    __threadfence();
+    if (atomicAdd(done, 1u) == gridDim.x - 1) {
+      *done = 0;
+      *reinterpret_cast<volatile uint32_t*>(mine + AR_CALLS_OFF) = call + 1;
+    }
+  }
+}
 
-  // 1. my chunk -> my slot
-  uint4* my_slot = reinterpret_cast<uint4*>(mine + AR_DATA_OFF + slot * p.slot_bytes);
-  for (int64_t i = v0 + threadIdx.x; i < v1; i += AR_THREADS) my_slot[i] = p.in[i];
+// block b of this rank <-> block b of every peer; `value` is the same on every rank and grows with every barrier
+template <int WORLD>
+__device__ __forceinline__ void ar_block_barrier(const ArParams& p, uint8_t* mine, int b, uint32_t value) {
   __syncthreads();  // (the release below orders the whole block's stores: cumulativity through the barrier)
-
-  // 2. per-block barrier with the same block of every peer
   if (threadIdx.x < WORLD && threadIdx.x != p.rank) {
     const int peer = threadIdx.x;
     __threadfence_system();
-    st_release_sys(reinterpret_cast<uint32_t*>(p.base[peer]) + b * AR_MAX_RANKS + p.rank, call);
+    st_release_sys(reinterpret_cast<uint32_t*>(p.base[peer]) + b * AR_MAX_RANKS + p.rank, value);
     const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine) + b * AR_MAX_RANKS + peer;
     const long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys(flag) - call) < 0) {
+    while ((int32_t)(ld_acquire_sys(flag) - value) < 0) {
       if (clock64() - t0 > 40000000000LL) {  // ~20 s: a peer is gone; report instead of hanging the GPU
         *reinterpret_cast<uint32_t*>(mine + AR_ERR_OFF) = 1;
         break;
@@ -101,7 +151,22 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_oneshot_kernel(const __g
     }
   }
   __syncthreads();
+}
 
+template <bool BF16, int WORLD>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_oneshot_kernel(const __grid_constant__ ArParams p) {
+  const int b = blockIdx.x;
+  uint8_t* mine = p.base[p.rank];
+  const uint32_t call = ar_call_number(mine);
+  const int slot = call & 1;
+  const int64_t per = (p.nvec + gridDim.x - 1) / gridDim.x;
+  const int64_t v0 = (int64_t)b * per, v1 = v0 + per < p.nvec ? v0 + per : p.nvec;
+
+  // 1. my chunk -> my slot
+  uint4* my_slot = reinterpret_cast<uint4*>(mine + AR_DATA_OFF + slot * p.slot_bytes);
+  for (int64_t i = v0 + threadIdx.x; i < v1; i += AR_THREADS) my_slot[i] = p.in[i];
+  // 2. per-block barrier with the same block of every peer
+  ar_block_barrier<WORLD>(p, mine, b, 2 * call + 1);
   // 3. reduce chunk b of every rank in rank order
   const uint4* src[WORLD];
 #pragma unroll
@@ -113,46 +178,22 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_oneshot_kernel(const __g
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int r = 0; r < WORLD; ++r) add8<BF16>(acc, v[r]);
-    p.out[i] = make_uint4(pack_half2<BF16>(acc[0], acc[1]), pack_half2<BF16>(acc[2], acc[3]), pack_half2<BF16>(acc[4], acc[5]),
-                          pack_half2<BF16>(acc[6], acc[7]));
+    p.out[i] = pack8<BF16>(acc);
   }
-  if (threadIdx.x == 0) {
-    *cnt = call;
-    *calls = *calls + 1;
-  }
+  ar_finish(mine, call);
 }
 
 // Two-shot variant for more ranks / larger messages (custom_all_reduce.cuh:300-400 picks the same way): rank r
 // reduces only chunk r (1/W of the message) from every rank, publishes it in place in its own slot, and all ranks
 // gather the W reduced chunks: 2 (W-1)/W of the message crosses NVLink per rank instead of (W-1) times the message.
 // Block b owns sub-range b of EVERY chunk in all three phases, so the per-block flag barrier still covers exactly
-// the data the block depends on.  Two barriers per call, two consecutive flag sequence numbers.
-template <int WORLD>
-__device__ __forceinline__ void ar_block_barrier(const ArParams& p, uint8_t* mine, int b, uint32_t value) {
-  if (threadIdx.x < WORLD && threadIdx.x != p.rank) {
-    const int peer = threadIdx.x;
-    __threadfence_system();
-    st_release_sys(reinterpret_cast<uint32_t*>(p.base[peer]) + b * AR_MAX_RANKS + p.rank, value);
-    const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine) + b * AR_MAX_RANKS + peer;
-    const long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys(flag) - value) < 0) {
-      if (clock64() - t0 > 40000000000LL) {
-        *reinterpret_cast<uint32_t*>(mine + AR_ERR_OFF) = 1;
-        break;
-      }
-    }
-  }
-  __syncthreads();
-}
-
+// the data the block depends on.
 template <bool BF16, int WORLD>
 __global__ void __launch_bounds__(AR_THREADS) allreduce_twoshot_kernel(const __grid_constant__ ArParams p) {
   const int b = blockIdx.x;
   uint8_t* mine = p.base[p.rank];
-  uint32_t* cnt = reinterpret_cast<uint32_t*>(mine + AR_CNT_OFF) + b;
-  uint32_t* calls = reinterpret_cast<uint32_t*>(mine + AR_CALLS_OFF) + b;
-  const uint32_t call = *cnt + 1;  // two barriers per call: flag values call and call + 1
-  const int slot = *calls & 1;
+  const uint32_t call = ar_call_number(mine);
+  const int slot = call & 1;
   const int64_t cv = (p.nvec + WORLD - 1) / WORLD;          // vectors per chunk
   const int64_t sv = (cv + gridDim.x - 1) / gridDim.x;      // vectors per (chunk, block)
   const int64_t j0 = (int64_t)b * sv, j1 = j0 + sv < cv ? j0 + sv : cv;
@@ -164,8 +205,7 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_twoshot_kernel(const __g
       const int64_t i = c * cv + j;
       if (i < p.nvec) my_slot[i] = p.in[i];
     }
-  __syncthreads();
-  ar_block_barrier<WORLD>(p, mine, b, call);
+  ar_block_barrier<WORLD>(p, mine, b, 2 * call + 1);
   // 2. reduce chunk `rank` in rank order, publish it in place
   const uint4* src[WORLD];
 #pragma unroll
@@ -179,16 +219,12 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_twoshot_kernel(const __g
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int r = 0; r < WORLD; ++r) add8<BF16>(acc, v[r]);
-    const uint4 o = make_uint4(pack_half2<BF16>(acc[0], acc[1]), pack_half2<BF16>(acc[2], acc[3]),
-                               pack_half2<BF16>(acc[4], acc[5]), pack_half2<BF16>(acc[6], acc[7]));
+    const uint4 o = pack8<BF16>(acc);
     my_slot[i] = o;
     p.out[i] = o;
   }
-  __syncthreads();
-  ar_block_barrier<WORLD>(p, mine, b, call + 1);
+  ar_block_barrier<WORLD>(p, mine, b, 2 * call + 2);
   // 3. gather the other ranks' reduced chunks: all W - 1 remote loads of a thread are issued before the first store
-  //    (volatile loads are not reordered across the stores by the compiler: chunk by chunk they were W - 1 serial
-  //    NVLink round trips)
   for (int64_t j = j0 + threadIdx.x; j < j1; j += AR_THREADS) {
     uint4 v[WORLD];
 #pragma unroll
@@ -202,17 +238,96 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_twoshot_kernel(const __g
       if (c != p.rank && i < p.nvec) p.out[i] = v[c];
     }
   }
-  if (threadIdx.x == 0) {
-    *cnt = call + 1;
-    *calls = *calls + 1;
+  ar_finish(mine, call);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// row layout: the message is [M rows x rowvec vectors]; block b owns rows [b * rpb, (b + 1) * rpb)
+// ---------------------------------------------------------------------------------------------------------------
+struct ArRows {
+  int M, rowvec, rpb;
+  int epi;  // 0: out = sum;  1: fused add + RMSNorm (+ quant) epilogue (RowNormArgs)
+};
+
+template <bool BF16, int WORLD, bool NVLS, int NV>
+__global__ void __launch_bounds__(AR_ROW_THREADS) allreduce_rows_kernel(const __grid_constant__ ArParams p, const ArRows r,
+                                                                        const RowNormArgs e) {
+  griddep_wait();
+  griddep_launch();
+  __shared__ float red[8];
+  const int b = blockIdx.x;
+  uint8_t* mine = p.base[p.rank];
+  const uint32_t call = ar_call_number(mine);
+  const int slot = call & 1;
+  const int row0 = b * r.rpb, row1 = min(r.M, row0 + r.rpb);
+  const int64_t v0 = (int64_t)row0 * r.rowvec;
+  const int64_t v1 = min((int64_t)row1 * r.rowvec, p.nvec);
+  const size_t slot_off = AR_DATA_OFF + (size_t)slot * p.slot_bytes;
+  const size_t stage_off = AR_DATA_OFF + (size_t)(2 + slot) * p.slot_bytes;
+
+  // 0. my rows -> my slot
+  uint4* my_slot = reinterpret_cast<uint4*>(mine + slot_off);
+  for (int64_t i = v0 + threadIdx.x; i < v1; i += AR_ROW_THREADS) my_slot[i] = p.in[i];
+  ar_block_barrier<WORLD>(p, mine, b, 2 * call + 1);
+
+  const uint4* x_src;  // where the epilogue finds the summed rows (NVLS), or nullptr (PULL: summed on the fly)
+  if constexpr (NVLS) {
+    // 1. sub-range `rank` of the block's rows: the switch reduces, the result is multicast into every out stage
+    const int64_t len = v1 - v0;
+    const int64_t sub = (len + WORLD - 1) / WORLD;
+    const int64_t a0 = v0 + p.rank * sub, a1 = min(a0 + sub, v1);
+    const uint4* mc_in = reinterpret_cast<const uint4*>(p.mc + slot_off);
+    uint4* mc_out = reinterpret_cast<uint4*>(p.mc + stage_off);
+    constexpr int U = 4;  // loads in flight per thread
+    for (int64_t i = a0 + threadIdx.x; i < a1; i += U * AR_ROW_THREADS) {
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (i + u * AR_ROW_THREADS < a1) v[u] = multimem_ld_reduce<BF16>(mc_in + i + u * AR_ROW_THREADS);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (i + u * AR_ROW_THREADS < a1) multimem_st(mc_out + i + u * AR_ROW_THREADS, v[u]);
+    }
+    ar_block_barrier<WORLD>(p, mine, b, 2 * call + 2);
+    x_src = reinterpret_cast<const uint4*>(mine + stage_off);
+  } else {
+    x_src = nullptr;
   }
+  const uint4* src[WORLD];
+#pragma unroll
+  for (int q = 0; q < WORLD; ++q) src[q] = reinterpret_cast<const uint4*>(p.base[q] + slot_off);
+  auto summed = [&](int64_t i) -> uint4 {
+    if constexpr (NVLS) {
+      return ld_volatile_v4(x_src + i);
+    } else {
+      uint4 v[WORLD];
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q) v[q] = ld_volatile_v4(src[q] + i);
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, v[q]);
+      return pack8<BF16>(acc);
+    }
+  };
+
+  // 2. epilogue over the block's full rows
+  if (r.epi == 0) {
+    for (int64_t i = v0 + threadIdx.x; i < v1; i += AR_ROW_THREADS) p.out[i] = summed(i);
+  } else {
+    for (int m = row0; m < row1; ++m) {
+      const int64_t rv = (int64_t)m * r.rowvec;
+      rmsnorm_quant_row<BF16, NV>(e, m, [&](int vec) { return summed(rv + vec); }, red);
+    }
+  }
+  ar_finish(mine, call);
 }
 
 struct ArContext {
   ArParams p;
-  void* own;
+  void* own;  // cudaMalloc'ed by b200_ar_alloc (freed by destroy) or nullptr when the caller owns the regions
   void* opened[AR_MAX_RANKS];
   int device;
+  int mode;   // -1 = measured policy (b200_ar_mode); 1 / 2 / 3 / 4 force a kernel (must be the same on every rank)
 };
 
 }  // namespace b200
@@ -221,7 +336,7 @@ using namespace b200;
 
 extern "C" size_t b200_ar_region_bytes(size_t max_message_bytes) {
   const size_t slot = (max_message_bytes + 255) & ~(size_t)255;
-  return AR_DATA_OFF + 2 * slot;
+  return AR_DATA_OFF + 4 * slot;
 }
 
 // allocate this rank's region (zeroed) and export its 64-byte IPC handle
@@ -234,13 +349,21 @@ extern "C" int b200_ar_alloc(size_t max_message_bytes, void** region_out, void* 
   B200_CUDA(cudaMemset(ptr, 0, bytes));
   B200_CUDA(cudaDeviceSynchronize());
   cudaIpcMemHandle_t h;
-  B200_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  const cudaError_t e = cudaIpcGetMemHandle(&h, ptr);
+  if (e != cudaSuccess) {
+    cudaFree(ptr);
+    return check_cuda(e, "cudaIpcGetMemHandle");
+  }
   memcpy(ipc_handle_out64, &h, 64);
   *region_out = ptr;
   return B200_OK;
 }
 
-// handles = world x 64 bytes in rank order (own entry ignored); returns an opaque context
+extern "C" void b200_ar_free_region(void* region) {
+  if (region) cudaFree(region);
+}
+
+// handles = world x 64 bytes in rank order (own entry ignored); returns an opaque context that owns `own_region`
 extern "C" int b200_ar_init(void* own_region, const void* handles, int rank, int world, size_t max_message_bytes,
                             void** ctx_out) {
   B200_REQUIRE(own_region && handles && ctx_out && world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, B200_ERR_ARG,
@@ -248,9 +371,11 @@ extern "C" int b200_ar_init(void* own_region, const void* handles, int rank, int
   ArContext* c = new ArContext();
   memset(c, 0, sizeof(*c));
   c->own = own_region;
+  c->mode = -1;
   cudaGetDevice(&c->device);
   c->p.rank = rank;
   c->p.world = world;
+  c->p.mc = nullptr;
   c->p.slot_bytes = (max_message_bytes + 255) & ~(size_t)255;
   for (int r = 0; r < world; ++r) {
     if (r == rank) {
@@ -276,11 +401,42 @@ extern "C" int b200_ar_init(void* own_region, const void* handles, int rank, int
   return B200_OK;
 }
 
+// The caller already holds mappings of every rank's region (e.g. a torch symmetric-memory rendezvous): `regions` is a
+// HOST array of `world` device pointers in rank order, each >= b200_ar_region_bytes(max_message_bytes) bytes and
+// zero-filled before the first call; `multicast` is the NVSwitch multicast address of the same buffer or NULL.
+// The context does not own the regions.
+extern "C" int b200_ar_init_ptrs(const uint64_t* regions, uint64_t multicast, int rank, int world, size_t max_message_bytes,
+                                 void** ctx_out) {
+  B200_REQUIRE(regions && ctx_out && world >= 2 && world <= AR_MAX_RANKS && rank >= 0 && rank < world, B200_ERR_ARG,
+               "ar_init_ptrs: need 2 <= world <= %d", AR_MAX_RANKS);
+  for (int r = 0; r < world; ++r)
+    B200_REQUIRE(regions[r] != 0 && (regions[r] & 255) == 0, B200_ERR_ARG, "ar_init_ptrs: region %d is null or misaligned", r);
+  ArContext* c = new ArContext();
+  memset(c, 0, sizeof(*c));
+  c->mode = -1;
+  cudaGetDevice(&c->device);
+  c->p.rank = rank;
+  c->p.world = world;
+  c->p.mc = (uint8_t*)(uintptr_t)multicast;
+  c->p.slot_bytes = (max_message_bytes + 255) & ~(size_t)255;
+  for (int r = 0; r < world; ++r) c->p.base[r] = (uint8_t*)(uintptr_t)regions[r];
+  *ctx_out = c;
+  return B200_OK;
+}
+
+extern "C" int b200_ar_has_multicast(void* ctx) { return ctx && ((ArContext*)ctx)->p.mc ? 1 : 0; }
+
+extern "C" int b200_ar_set_mode(void* ctx, int mode) {
+  B200_REQUIRE(ctx && mode >= -1 && mode <= 4, B200_ERR_ARG, "ar_set_mode: mode must be -1 (policy) or 1..4");
+  ((ArContext*)ctx)->mode = mode;
+  return B200_OK;
+}
+
 extern "C" int b200_ar_error(void* ctx) {
   ArContext* c = (ArContext*)ctx;
   if (!c) return -1;
   uint32_t v = 0;
-  if (cudaMemcpy(&v, (uint8_t*)c->own + AR_ERR_OFF, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  if (cudaMemcpy(&v, c->p.base[c->p.rank] + AR_ERR_OFF, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
   return (int)v;
 }
 
@@ -289,21 +445,76 @@ extern "C" void b200_ar_destroy(void* ctx) {
   if (!c) return;
   for (int r = 0; r < AR_MAX_RANKS; ++r)
     if (c->opened[r]) cudaIpcCloseMemHandle(c->opened[r]);
-  cudaFree(c->own);
+  if (c->own) cudaFree(c->own);
   delete c;
 }
 
-// Which path is fastest for a message, measured on 2 / 4 / 8 B200 of one NVSwitch box (tools/ar_check.py AR_SWEEP=1,
-// profiles/r01b_allreduce.md): 1 = one-shot, 2 = two-shot, 0 = leave it to ncclAllReduce.  The reference makes the same
-// kind of split (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one stage, else two).
-extern "C" int b200_ar_mode(int world, size_t bytes) {
+// Which kernel is fastest for a plain all-reduce, measured on 2 / 4 / 8 B200 of one NVSwitch box (tools/ar_check.py
+// AR_SWEEP=1; profiles/r01b_allreduce.md, profiles/r02_allreduce.md):
+//   1 = one-shot (flat), 2 = two-shot (flat, peer loads), 3 = rows kernel with NVLS multicast (needs a multicast
+//   mapping), 4 = rows kernel, one-shot pull; 0 = leave it to ncclAllReduce.
+// `multicast` = the context has a multicast mapping.  The reference makes the same kind of split
+// (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one stage, else two).
+extern "C" int b200_ar_mode2(int world, size_t bytes, int multicast) {
   if (world < 2 || world > AR_MAX_RANKS) return 0;
   if (world == 2) return 1;
+  if (multicast) {
+    if (world <= 4) return bytes <= ((size_t)1 << 20) ? 1 : 3;
+    return bytes <= ((size_t)256 << 10) ? 1 : 3;
+  }
   if (world <= 4) return bytes <= ((size_t)6 << 20) ? 1 : 2;
   if (bytes <= (size_t)1536 * 1024) return 1;
   if (bytes < ((size_t)3 << 20)) return 0;
   return 2;
 }
+extern "C" int b200_ar_mode(int world, size_t bytes) { return b200_ar_mode2(world, bytes, 0); }
+
+namespace {
+
+template <bool NVLS, int NV>
+int launch_rows_w(const ArParams& p, const ArRows& r, const RowNormArgs& e, int nb, bool bf16, cudaStream_t st) {
+#define B200_ARR(W)                                                                                                          \
+  case W:                                                                                                                    \
+    if (bf16) launch_pdl(allreduce_rows_kernel<true, W, NVLS, NV>, dim3(nb), dim3(AR_ROW_THREADS), 0, st, p, r, e);          \
+    else launch_pdl(allreduce_rows_kernel<false, W, NVLS, NV>, dim3(nb), dim3(AR_ROW_THREADS), 0, st, p, r, e);              \
+    break;
+  switch (p.world) {
+    B200_ARR(2) B200_ARR(3) B200_ARR(4) B200_ARR(5) B200_ARR(6) B200_ARR(7) B200_ARR(8)
+    default:
+      set_error("ar: world %d", p.world);
+      return B200_ERR_UNSUPPORTED;
+  }
+#undef B200_ARR
+  return launched("allreduce_rows_kernel launch");
+}
+
+// rows kernel: M rows of rowvec vectors (the last row may be short when epi == 0)
+int launch_rows(const ArContext* c, ArParams p, int M, int rowvec, int epi, const RowNormArgs& e, bool nvls, bool bf16,
+                cudaStream_t st) {
+  // enough blocks that a block's share of a reduce-scatter (1 / world of its rows) still fills its 256 threads;
+  // a function of the sizes only, so every rank launches the same grid
+  int64_t per_block_vec = (int64_t)AR_ROW_THREADS * (nvls ? p.world : 1);
+  int rpb = (int)((per_block_vec + rowvec - 1) / rowvec);
+  if (rpb < 1) rpb = 1;
+  int nb = (M + rpb - 1) / rpb;
+  if (nb > AR_MAX_BLOCKS) {
+    rpb = (M + AR_MAX_BLOCKS - 1) / AR_MAX_BLOCKS;
+    nb = (M + rpb - 1) / rpb;
+  }
+  ArRows r;
+  r.M = M; r.rowvec = rowvec; r.rpb = rpb; r.epi = epi;
+  const int nv = epi ? (rowvec + 255) / 256 : 1;
+  if (nvls) {
+    if (nv <= 1) return launch_rows_w<true, 1>(p, r, e, nb, bf16, st);
+    if (nv <= 2) return launch_rows_w<true, 2>(p, r, e, nb, bf16, st);
+    return launch_rows_w<true, 4>(p, r, e, nb, bf16, st);
+  }
+  if (nv <= 1) return launch_rows_w<false, 1>(p, r, e, nb, bf16, st);
+  if (nv <= 2) return launch_rows_w<false, 2>(p, r, e, nb, bf16, st);
+  return launch_rows_w<false, 4>(p, r, e, nb, bf16, st);
+}
+
+}  // namespace
 
 // in / out: n_elems 16-bit values, 16-byte aligned, n_elems % 8 == 0, n_elems * 2 <= max_message_bytes; out may alias in
 extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int dtype, void* stream) {
@@ -318,23 +529,21 @@ extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n
   p.in = (const uint4*)in;
   p.out = (uint4*)out;
   p.nvec = n_elems / 8;
-  // enough blocks to keep NVLink reads in flight; the block count must be the same on every rank (it is a function
-  // of the message size only) because block b pairs with block b of the peers
-  int64_t nb = (p.nvec + AR_THREADS - 1) / AR_THREADS;  // one 16-byte vector per thread up to 1 MiB: latency, not bandwidth, bounds these sizes
-  if (nb > AR_MAX_BLOCKS) nb = AR_MAX_BLOCKS;
-  if (nb < 1) nb = 1;
   cudaStream_t st = (cudaStream_t)stream;
-  // a function of (world, size) only, so every rank picks the same kernel
-  bool two_shot = b200_ar_mode(p.world, (size_t)n_elems * 2) == 2;
-  {
-    static int mode = -1;  // developer override: B200_AR_MODE=1 one-shot, 2 two-shot (must be the same on every rank)
-    if (mode < 0) { const char* e = getenv("B200_AR_MODE"); mode = e ? atoi(e) : 0; }
-    if (mode == 1) two_shot = false;
-    if (mode == 2 && p.world > 2) two_shot = true;
+  // a function of (world, size, multicast) only, so every rank picks the same kernel
+  int mode = c->mode > 0 ? c->mode : b200_ar_mode2(p.world, (size_t)n_elems * 2, p.mc != nullptr);
+  if (mode == 3 && !p.mc) mode = 2;
+  if (mode == 2 && p.world == 2) mode = 1;
+  if (mode == 0) mode = p.world <= 4 ? 1 : 2;  // the caller asked for this path although the policy prefers NCCL
+  if (mode == 3 || mode == 4) {
+    const int rowvec = 512;  // 8 KB pseudo-rows
+    const int M = (int)((p.nvec + rowvec - 1) / rowvec);
+    RowNormArgs e = {};
+    return launch_rows(c, p, M, rowvec, 0, e, mode == 3, dtype == B200_BF16, st);
   }
-  if (two_shot) {
+  if (mode == 2) {
     int64_t nb2 = ((p.nvec + p.world - 1) / p.world + AR_THREADS - 1) / AR_THREADS;
-    if (nb2 > AR_MAX_BLOCKS) nb2 = AR_MAX_BLOCKS;
+    if (nb2 > AR_FLAT_BLOCKS) nb2 = AR_FLAT_BLOCKS;
     if (nb2 < 1) nb2 = 1;
 #define B200_AR2(W)                                                                                      \
   case W:                                                                                                \
@@ -350,6 +559,11 @@ extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n
 #undef B200_AR2
     return launched("allreduce_twoshot_kernel launch");
   }
+  // enough blocks to keep NVLink reads in flight; the block count must be the same on every rank (it is a function
+  // of the message size only) because block b pairs with block b of the peers
+  int64_t nb = (p.nvec + AR_THREADS - 1) / AR_THREADS;  // one 16-byte vector per thread up to 1 MiB: latency, not bandwidth, bounds these sizes
+  if (nb > AR_FLAT_BLOCKS) nb = AR_FLAT_BLOCKS;
+  if (nb < 1) nb = 1;
 #define B200_AR(W)                                                                        \
   case W:                                                                                 \
     if (dtype == B200_BF16) allreduce_oneshot_kernel<true, W><<<(unsigned)nb, AR_THREADS, 0, st>>>(p); \
@@ -363,4 +577,40 @@ extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n
   }
 #undef B200_AR
   return launched("allreduce_oneshot_kernel launch");
+}
+
+// all-reduce(sum) of in [M, H] fused with what follows a row-parallel linear in a decoder layer
+// (flashinfer_comm_fusion.py:122 flashinfer_allreduce_add_rmsnorm; layernorm.py forward with residual):
+//   x = sum over ranks (rounded to the half type, as the plain all-reduce writes it)
+//   residual += x (stored back);  y = RMSNorm(residual) * weight
+//   norm_out = y (optional);  (q, s) = per_token_group_quant_fp8(y, 128) (optional)
+// Bit-identical to b200_ar_allreduce followed by b200_rmsnorm_quant_fp8 when the one-shot pull kernel runs; with NVLS
+// the switch's fp32 accumulation order is not the rank order (results still identical on every rank).
+extern "C" int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* residual, const void* weight, void* norm_out,
+                                             void* q, int64_t q_sm, float* s, int64_t s_sm, int64_t s_sg, int M, int H,
+                                             int dtype, float eps, float q_eps, float fp8_min, float fp8_max, void* stream) {
+  ArContext* c = (ArContext*)ctx;
+  B200_REQUIRE(c && in && residual && weight && (norm_out || (q && s)) && M > 0 && H > 0, B200_ERR_ARG, "ar_allreduce_add_rmsnorm: bad argument");
+  B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, B200_ERR_UNSUPPORTED, "ar_allreduce_add_rmsnorm: dtype must be bf16/f16");
+  B200_REQUIRE(H % 128 == 0 && H <= 8192, B200_ERR_UNSUPPORTED, "ar_allreduce_add_rmsnorm: H must be a multiple of 128, at most 8192 (got %d)", H);
+  B200_REQUIRE((size_t)M * H * 2 <= c->p.slot_bytes, B200_ERR_UNSUPPORTED, "ar_allreduce_add_rmsnorm: message of %zu bytes exceeds the %zu-byte slots",
+               (size_t)M * H * 2, c->p.slot_bytes);
+  B200_REQUIRE(((uintptr_t)in & 15) == 0 && ((uintptr_t)residual & 15) == 0 && ((uintptr_t)weight & 15) == 0 &&
+                   (!norm_out || ((uintptr_t)norm_out & 15) == 0) && (!q || (((uintptr_t)q & 7) == 0 && q_sm % 8 == 0)),
+               B200_ERR_ARG, "ar_allreduce_add_rmsnorm: operands must be 16-byte aligned");
+  ArParams p = c->p;
+  p.in = (const uint4*)in;
+  p.out = nullptr;
+  p.nvec = (int64_t)M * H / 8;
+  const size_t bytes = (size_t)M * H * 2;
+  int mode = c->mode > 0 ? c->mode : b200_ar_mode2(p.world, bytes, p.mc != nullptr);
+  bool nvls = (mode == 3) && p.mc;
+  if (!nvls && c->mode <= 0 && p.world > 4 && bytes > ((size_t)1536 << 10)) {
+    set_error("ar_allreduce_add_rmsnorm: %zu bytes at %d ranks without a multicast mapping: run the two kernels", bytes, p.world);
+    return B200_ERR_UNSUPPORTED;
+  }
+  RowNormArgs e;
+  e.residual = (uint16_t*)residual; e.w = (const uint16_t*)weight; e.out = (uint16_t*)norm_out; e.q = (uint8_t*)q; e.q_sm = q_sm;
+  e.s = s; e.s_sm = s_sm; e.s_sg = s_sg; e.H = H; e.eps = eps; e.q_eps = q_eps; e.fmin_ = fp8_min; e.fmax_ = fp8_max;
+  return launch_rows(c, p, M, H / 8, 1, e, nvls, dtype == B200_BF16, (cudaStream_t)stream);
 }

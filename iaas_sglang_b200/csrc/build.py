@@ -16,13 +16,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 SO = os.path.join(HERE, "libb200sgl.so")
 SOURCES = ["runtime.cu", "elementwise.cu", "decode_attn.cu", "extend_attn.cu", "gemm_tc.cu", "gemm_skinny.cu", "gemm_big.cu", "awq_gemm.cu", "awq_fused.cu", "fused_elem.cu", "allreduce.cu"]
-HEADERS = ["common.cuh", "gemm_skinny.h", "decode_mla.cuh", os.path.join(ROOT, "include", "b200_sgl.h")]
+HEADERS = ["common.cuh", "gemm_skinny.h", "decode_mla.cuh", "rmsnorm_row.cuh", os.path.join(ROOT, "include", "b200_sgl.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--use_fast_math_off_placeholder",
-]
-FLAGS = [f for f in FLAGS if f != "--use_fast_math_off_placeholder"]
-FLAGS += ["-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
+         "--expt-relaxed-constexpr"]
 FLAGS += os.environ.get("B200_NVCC_EXTRA", "").split()
 
 
@@ -49,11 +46,27 @@ def _compile(src: str, verbose: bool):
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    """Serialised across processes (torchrun starts N ranks that may all find the sources newer): an exclusive
+    file lock around the whole build, objects and the link go to temporary names and are renamed into place, so a
+    rank that is dlopen-ing the library never sees a half-written file."""
+    import fcntl
+
     if not force and up_to_date():
         return SO
     if not os.path.exists(NVCC):
         raise RuntimeError(f"nvcc not found at {NVCC}; cannot build {SO}")
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    with open(os.path.join(HERE, "build", ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and up_to_date():   # another process built it while we waited
+                return SO
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
     t0 = time.time()
     with ThreadPoolExecutor(max_workers=8) as ex:
         results = list(ex.map(lambda s: _compile(s, verbose), sources()))
@@ -64,10 +77,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if rc != 0:
             raise RuntimeError(f"nvcc failed on {src}")
         objs.append(obj)
-    cmd = [NVCC, "-shared", "-o", SO, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "shared"]
+    tmp = f"{SO}.{os.getpid()}.tmp"
+    cmd = [NVCC, "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "shared"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")
+    os.replace(tmp, SO)
     if verbose:
         sys.stderr.write(f"built {SO} in {time.time() - t0:.1f}s\n")
     return SO

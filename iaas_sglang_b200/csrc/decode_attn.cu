@@ -59,9 +59,15 @@ struct DecodeKParams {
   float* part_lse;  // generic path: [B, Hq, S];      tuned path: [grid, 2, HPC*16]   (log2 domain)
   const void* r2t;
   int64_t r2t_stride;
-  const int64_t* rpi;
-  const int64_t* seq_lens;
-  const int64_t* loc;
+  const void* rpi;       // [B] int64 or int32 (meta32 bit 1); nullptr = identity (row b of the table is request b)
+  const void* seq_lens;  // [B] int64 or int32 (meta32 bit 0)
+  const void* loc;       // [B] int64 or int32 (meta32 bit 2)
+  int meta32;
+  int page_shift;        // table entries are page ids of 1 << page_shift tokens (0 = token slots, req_to_token)
+  const uint16_t* q_pe;  // MLA: rope part of q [B, Hq, 64] when q holds only the 512 latent columns (cutlass_mla_decode)
+  int64_t qpe_sb, qpe_sh;
+  const uint16_t* k_pe_new;  // MLA: rope part of the new latent row when k_new holds only the 512 latent columns
+  int64_t kpe_sb;
   int idx64;
   int B, Hq, Hkv, G, D, Dv;
   int num_splits;
@@ -70,6 +76,14 @@ struct DecodeKParams {
   float sm_scale, logit_cap;
   MergeQuant mq;
 };
+
+// seq_lens / req_pool_indices / out_cache_loc arrive as int64 (schedule_batch.py) or int32 (cuda_graph_runner.py:273-276)
+__device__ __forceinline__ int64_t meta_at(const void* p, int64_t i, bool is32) {
+  return is32 ? (int64_t) reinterpret_cast<const int32_t*>(p)[i] : reinterpret_cast<const int64_t*>(p)[i];
+}
+__device__ __forceinline__ int64_t seq_len_at(const DecodeKParams& p, int b) { return meta_at(p.seq_lens, b, p.meta32 & 1); }
+__device__ __forceinline__ int64_t req_at(const DecodeKParams& p, int b) { return p.rpi ? meta_at(p.rpi, b, p.meta32 & 2) : (int64_t)b; }
+__device__ __forceinline__ int64_t loc_at(const DecodeKParams& p, int b) { return meta_at(p.loc, b, p.meta32 & 4); }
 
 constexpr int kMaxSmem = 232448;  // 227 KB: the sm_100 per-block opt-in limit
 constexpr int kMaxBatchTable = 1024;
@@ -170,11 +184,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
   griddep_wait();    // programmatic dependent launch: q / k_new / the batch tensors belong to the stream order
   griddep_launch();  // the merge kernel may be scheduled as soon as SM resources free up
   for (int b = threadIdx.x; b < p.B; b += kAttnThreads) {
-    int64_t len = p.seq_lens[b];
+    int64_t len = seq_len_at(p, b);
     if (len < 0) len = 0;
     s_len[b] = (int32_t)len;
-    s_rpi[b] = (int32_t)p.rpi[b];
-    s_loc[b] = p.fused_new ? p.loc[b] : -1;
+    s_rpi[b] = (int32_t)req_at(p, b);
+    s_loc[b] = p.fused_new ? loc_at(p, b) : -1;
     s_P[b + 1] = (int32_t)((len + C::TILE_T - 1) / C::TILE_T);
   }
   if (threadIdx.x == 0) {
@@ -563,7 +577,7 @@ template <bool BF16, int NV, bool QUANT>
 __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __restrict__ part_o,
                                                                 const float* __restrict__ part_lse,
                                                                 uint16_t* out,
-                                                                const int64_t* __restrict__ seq_lens, int B, int Hq,
+                                                                const void* __restrict__ seq_lens, int lens32, int B, int Hq,
                                                                 int Ggrp, int HPC, int tile_t, int NG, int n_qblk,
                                                                 int grid, int Dv, const MergeQuant mq) {
   griddep_wait();
@@ -574,7 +588,7 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   if (h >= Hq) return;
   int all = 0, before = 0, tiles_b = 0;
   for (int i = lane; i < B; i += 32) {
-    int64_t len = seq_lens[i];
+    int64_t len = meta_at(seq_lens, i, lens32);
     if (len < 0) len = 0;
     const int tl = (int)((len + tile_t - 1) / tile_t);
     all += tl;
@@ -687,13 +701,13 @@ template <bool BF16>
 static int launch_merge_part(const DecodeKParams& kp, int Ggrp, int HPC, int tile_t, int NG, int n_qblk, int grid, cudaStream_t st) {
   const dim3 g(kp.B * ((kp.Hq + 7) / 8)), blk(256);
   if (kp.mq.q)  // Dv == 128 and an 8-byte aligned `out` were checked by the entry point
-    launch_pdl(decode_merge_part_kernel<BF16, 1, true>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp,
+    launch_pdl(decode_merge_part_kernel<BF16, 1, true>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.meta32 & 1, kp.B, kp.Hq, Ggrp,
                HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
   else if (kp.Dv <= 128)
-    launch_pdl(decode_merge_part_kernel<BF16, 1, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp,
+    launch_pdl(decode_merge_part_kernel<BF16, 1, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.meta32 & 1, kp.B, kp.Hq, Ggrp,
                HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
   else
-    launch_pdl(decode_merge_part_kernel<BF16, 4, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.B, kp.Hq, Ggrp,
+    launch_pdl(decode_merge_part_kernel<BF16, 4, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.meta32 & 1, kp.B, kp.Hq, Ggrp,
                HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
   return launched("decode_merge_part_kernel launch");
 }
@@ -708,8 +722,9 @@ __global__ void __launch_bounds__(128) decode_attn_generic_kernel(const __grid_c
   const int split = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / p.G;
   const int D = p.D, Dv = p.Dv;
-  const int64_t len = p.seq_lens[b], req = p.rpi[b];
-  const int64_t loc_b = p.fused_new ? p.loc[b] : -1;
+  const int64_t len = seq_len_at(p, b), req = req_at(p, b);
+  const int64_t loc_b = p.fused_new ? loc_at(p, b) : -1;
+  const int64_t page_mask = ((int64_t)1 << p.page_shift) - 1;
   const int64_t per = (len + p.num_splits - 1) / p.num_splits;
   const int64_t kv0 = (int64_t)split * per;
   const int64_t kv1 = (kv0 + per < len) ? kv0 + per : len;
@@ -732,13 +747,18 @@ __global__ void __launch_bounds__(128) decode_attn_generic_kernel(const __grid_c
 #pragma unroll
   for (int e = 0; e < MAXE; ++e) {
     const int d = e * 32 + lane;
-    qr[e] = d < D ? half_to_float<BF16>(p.q[b * p.q_sb + (int64_t)h * p.q_sh + d]) : 0.f;
+    qr[e] = 0.f;
+    if (d < D) {
+      const uint16_t* qp = (p.q_pe && d >= Dv) ? p.q_pe + b * p.qpe_sb + (int64_t)h * p.qpe_sh + (d - Dv)
+                                               : p.q + b * p.q_sb + (int64_t)h * p.q_sh + d;
+      qr[e] = half_to_float<BF16>(*qp);
+    }
     acc[e] = 0.f;
   }
   float m_run = -INFINITY, l_run = 0.f;
   const bool has_cap = p.logit_cap > 0.f;
   for (int64_t pos = kv0 + warp; pos < kv1; pos += 4) {
-    const int64_t idx = load_index(p.r2t, req * p.r2t_stride + pos, p.idx64);
+    const int64_t idx = (load_index(p.r2t, req * p.r2t_stride + (pos >> p.page_shift), p.idx64) << p.page_shift) + (pos & page_mask);
     const uint16_t* kr = p.k_buf + idx * p.kb_st + kvh * p.kb_sh;
     const uint16_t* vr = p.v_buf + idx * p.vb_st + kvh * p.vb_sh;
     if (idx == loc_b) {
@@ -820,15 +840,20 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const float* __restri
 }
 
 // KVCache.set_kv_buffer (memory_pool.py:418-456 / decode.cpp:771-809): grid = (B, Hkv), 16-bit elements
+// k_pe (MLA, set_mla_kv_buffer memory_pool.py:859-876): columns [D - Dpe, D) of the row come from k_pe [B, Dpe]
 __global__ void set_kv_kernel(uint16_t* k_buf, int64_t kb_st, int64_t kb_sh, uint16_t* v_buf, int64_t vb_st,
                               int64_t vb_sh, const uint16_t* k_new, int64_t kn_sb, int64_t kn_sh, const uint16_t* v_new,
-                              int64_t vn_sb, int64_t vn_sh, const int64_t* loc, int D, int Dv) {
+                              int64_t vn_sb, int64_t vn_sh, const void* loc, int loc32, int D, int Dv,
+                              const uint16_t* k_pe, int64_t kpe_sb, int Dpe) {
   const int b = blockIdx.x, h = blockIdx.y;
-  const int64_t l = loc[b];
+  const int64_t l = meta_at(loc, b, loc32);
   if (k_new) {
     const uint16_t* s = k_new + b * kn_sb + h * kn_sh;
     uint16_t* d = k_buf + l * kb_st + h * kb_sh;
-    for (int i = threadIdx.x; i < D; i += blockDim.x) d[i] = s[i];
+    const int Dn = k_pe ? D - Dpe : D;
+    for (int i = threadIdx.x; i < Dn; i += blockDim.x) d[i] = s[i];
+    if (k_pe)
+      for (int i = threadIdx.x; i < Dpe; i += blockDim.x) d[Dn + i] = k_pe[b * kpe_sb + i];
   }
   if (v_new) {
     const uint16_t* s = v_new + b * vn_sb + h * vn_sh;
@@ -935,7 +960,7 @@ extern "C" int b200_set_kv_buffer(void* k_buf, int64_t kb_st, int64_t kb_sh, voi
   if (B == 0) return B200_OK;
   set_kv_kernel<<<dim3(B, Hkv), 128, 0, (cudaStream_t)stream>>>(
       (uint16_t*)k_buf, kb_st, kb_sh, (uint16_t*)v_buf, vb_st, vb_sh, (const uint16_t*)k_new, kn_sb, kn_sh,
-      (const uint16_t*)v_new, vn_sb, vn_sh, loc, D, Dv);
+      (const uint16_t*)v_new, vn_sb, vn_sh, loc, 0, D, Dv, nullptr, 0, 0);
   return launched("set_kv_kernel launch");
 }
 
@@ -945,8 +970,12 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
   B200_REQUIRE(a->Hq % a->Hkv == 0, B200_ERR_ARG, "decode_attn: Hq %% Hkv != 0");
   B200_REQUIRE(a->dtype == B200_BF16 || a->dtype == B200_F16, B200_ERR_UNSUPPORTED, "decode_attn: dtype must be bf16/f16");
   B200_REQUIRE(a->D <= 1024 && a->Dv <= 1024, B200_ERR_UNSUPPORTED, "decode_attn: head dim > 1024");
-  B200_REQUIRE(a->q && a->k_buf && a->v_buf && a->out && a->req_to_token && a->req_pool_indices && a->seq_lens,
-               B200_ERR_ARG, "decode_attn: null tensor");
+  B200_REQUIRE(a->q && a->k_buf && a->v_buf && a->out && a->req_to_token && a->seq_lens, B200_ERR_ARG, "decode_attn: null tensor");
+  int page_shift = 0;
+  if (a->page_size > 1) {
+    B200_REQUIRE((a->page_size & (a->page_size - 1)) == 0, B200_ERR_UNSUPPORTED, "decode_attn: page_size %d is not a power of two", a->page_size);
+    while ((1 << page_shift) < a->page_size) ++page_shift;
+  }
   if (a->B == 0) return B200_OK;
   const int arch = b200_sm_arch();
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "decode_attn: requires an sm_100 device (got sm_%d); no fallback", arch);
@@ -967,12 +996,16 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
   kp.out = (uint16_t*)a->out;
   kp.r2t = a->req_to_token; kp.r2t_stride = a->req_to_token_stride; kp.idx64 = a->idx_is_i64;
   kp.rpi = a->req_pool_indices; kp.seq_lens = a->seq_lens; kp.loc = a->out_cache_loc;
+  kp.meta32 = a->meta_i32_mask & 7; kp.page_shift = page_shift;
+  kp.q_pe = (const uint16_t*)a->q_rope; kp.qpe_sb = a->qrope_stride_b; kp.qpe_sh = a->qrope_stride_h;
+  kp.k_pe_new = (const uint16_t*)a->k_rope_new; kp.kpe_sb = a->krope_stride_b;
+  B200_REQUIRE(is_mla || (!a->q_rope && !a->k_rope_new), B200_ERR_ARG, "decode_attn: q_rope / k_rope_new are MLA arguments");
   kp.B = a->B; kp.Hq = a->Hq; kp.Hkv = a->Hkv; kp.G = a->Hq / a->Hkv; kp.D = a->D; kp.Dv = a->Dv;
   kp.is_mla = is_mla; kp.sm_scale = a->sm_scale; kp.logit_cap = a->logit_cap;
   kp.mq = MergeQuant{};
 
   // tuned path needs 16-byte aligned, head-contiguous rows
-  bool mma = mma_path_ok(a->Hq, a->Hkv, a->D, a->Dv);
+  bool mma = mma_path_ok(a->Hq, a->Hkv, a->D, a->Dv) && page_shift == 0;
   int hpc = pick_hpc(a->Hkv);
   if (mma) {
     auto al16 = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
@@ -994,14 +1027,17 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
   bool mla = mla_path_ok(a->Hkv, a->D, a->Dv, is_mla) && a->num_splits <= 1;
   if (mla) {
     const bool rows_ok = ((uintptr_t)a->k_buf & 15) == 0 && a->kbuf_stride_t % 8 == 0;
-    const bool q_ok = ((uintptr_t)a->q & 3) == 0 && a->q_stride_b % 2 == 0 && a->q_stride_h % 2 == 0;
+    bool q_ok = ((uintptr_t)a->q & 3) == 0 && a->q_stride_b % 2 == 0 && a->q_stride_h % 2 == 0;
+    if (a->q_rope) q_ok = q_ok && ((uintptr_t)a->q_rope & 3) == 0 && a->qrope_stride_b % 2 == 0 && a->qrope_stride_h % 2 == 0;
     if (!rows_ok || !q_ok) mla = false;
   }
   // fused append (write_kv == 2) needs aligned, head-contiguous new rows on the tuned path
   bool fused = (write_kv == 2);
   if (fused && mla) {
     if (((uintptr_t)a->k_new & 15) != 0 || a->knew_stride_b % 8 != 0) fused = false;
+    if (a->k_rope_new && (((uintptr_t)a->k_rope_new & 15) != 0 || a->krope_stride_b % 8 != 0)) fused = false;
   }
+  if (fused && !mla && a->k_rope_new) fused = false;  // only the tuned MLA kernel substitutes a two-piece row
   if (fused && mma) {
     auto al16 = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
     const bool new_ok = al16(a->k_new) && al16(a->v_new) && a->knew_stride_b % 8 == 0 && a->vnew_stride_b % 8 == 0 &&
@@ -1010,11 +1046,12 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
     if (!new_ok) fused = false;
   }
   if (write_kv && !fused) {
-    int rc = b200_set_kv_buffer(a->k_buf, a->kbuf_stride_t, a->kbuf_stride_h, a->v_buf, a->vbuf_stride_t,
-                                a->vbuf_stride_h, a->k_new, a->knew_stride_b, a->knew_stride_h,
-                                is_mla ? nullptr : a->v_new, a->vnew_stride_b, a->vnew_stride_h, a->out_cache_loc,
-                                a->B, a->Hkv, a->D, a->Dv, 2, stream);
-    if (rc != 0) return rc;
+    set_kv_kernel<<<dim3(a->B, a->Hkv), 128, 0, st>>>(
+        (uint16_t*)a->k_buf, a->kbuf_stride_t, a->kbuf_stride_h, (uint16_t*)a->v_buf, a->vbuf_stride_t, a->vbuf_stride_h,
+        (const uint16_t*)a->k_new, a->knew_stride_b, a->knew_stride_h, is_mla ? nullptr : (const uint16_t*)a->v_new,
+        a->vnew_stride_b, a->vnew_stride_h, a->out_cache_loc, (a->meta_i32_mask >> 2) & 1, a->D, a->Dv,
+        (const uint16_t*)a->k_rope_new, a->krope_stride_b, a->D - a->Dv);
+    if (int rc = launched("set_kv_kernel launch")) return rc;
   }
   kp.fused_new = fused ? 1 : 0;
 
@@ -1031,9 +1068,14 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
       c.q = kp.q + (int64_t)b0 * kp.q_sb;
       if (kp.k_new) c.k_new = kp.k_new + (int64_t)b0 * kp.kn_sb;
       c.out = kp.out + (int64_t)b0 * kp.Hq * kp.Dv;
-      c.rpi = kp.rpi + b0;
-      c.seq_lens = kp.seq_lens + b0;
-      if (kp.loc) c.loc = kp.loc + b0;
+      if (kp.q_pe) c.q_pe = kp.q_pe + (int64_t)b0 * kp.qpe_sb;
+      if (kp.k_pe_new) c.k_pe_new = kp.k_pe_new + (int64_t)b0 * kp.kpe_sb;
+      if (b0 > 0) {
+        B200_REQUIRE(kp.rpi != nullptr, B200_ERR_UNSUPPORTED, "decode_attn: B > %d needs req_pool_indices", kMaxBatchTable);
+        c.rpi = (const uint8_t*)kp.rpi + (size_t)b0 * ((kp.meta32 & 2) ? 4 : 8);
+        c.seq_lens = (const uint8_t*)kp.seq_lens + (size_t)b0 * ((kp.meta32 & 1) ? 4 : 8);
+        if (kp.loc) c.loc = (const uint8_t*)kp.loc + (size_t)b0 * ((kp.meta32 & 4) ? 4 : 8);
+      }
       const int rc = a->dtype == B200_BF16 ? launch_mla<true>(c, st) : launch_mla<false>(c, st);
       if (rc != 0) return rc;
     }
@@ -1054,9 +1096,12 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
       if (kp.k_new) c.k_new = kp.k_new + (int64_t)b0 * kp.kn_sb;
       if (kp.v_new) c.v_new = kp.v_new + (int64_t)b0 * kp.vn_sb;
       c.out = kp.out + (int64_t)b0 * kp.Hq * kp.Dv;
-      c.rpi = kp.rpi + b0;
-      c.seq_lens = kp.seq_lens + b0;
-      if (kp.loc) c.loc = kp.loc + b0;
+      if (b0 > 0) {
+        B200_REQUIRE(kp.rpi != nullptr, B200_ERR_UNSUPPORTED, "decode_attn: B > %d needs req_pool_indices", kMaxBatchTable);
+        c.rpi = (const uint8_t*)kp.rpi + (size_t)b0 * ((kp.meta32 & 2) ? 4 : 8);
+        c.seq_lens = (const uint8_t*)kp.seq_lens + (size_t)b0 * ((kp.meta32 & 1) ? 4 : 8);
+        if (kp.loc) c.loc = (const uint8_t*)kp.loc + (size_t)b0 * ((kp.meta32 & 4) ? 4 : 8);
+      }
       if (kp.mq.q) {
         c.mq.q = kp.mq.q + (int64_t)b0 * kp.mq.q_sm;
         c.mq.s = kp.mq.s + (int64_t)b0 * kp.mq.s_sm;

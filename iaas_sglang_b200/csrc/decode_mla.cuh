@@ -60,11 +60,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_mla_mma_kernel(const _
   const int NG = n_qblk;
 
   for (int b = threadIdx.x; b < p.B; b += kAttnThreads) {
-    int64_t len = p.seq_lens[b];
+    int64_t len = seq_len_at(p, b);
     if (len < 0) len = 0;
     s_len[b] = (int32_t)len;
-    s_rpi[b] = (int32_t)p.rpi[b];
-    s_loc[b] = p.fused_new ? p.loc[b] : -1;
+    s_rpi[b] = (int32_t)req_at(p, b);
+    s_loc[b] = p.fused_new ? loc_at(p, b) : -1;
     s_P[b + 1] = (int32_t)((len + C::TILE_T - 1) / C::TILE_T);
   }
   if (threadIdx.x == 0) {
@@ -114,17 +114,25 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_mla_mma_kernel(const _
       const int64_t kv_end = (int64_t)(cur.tile + n) * C::TILE_T;
       const int64_t kv1 = kv_end < len ? kv_end : len;
       const uint16_t* knew_row = p.k_new + b * p.kn_sb;
+      const uint16_t* kpe_row = p.k_pe_new ? p.k_pe_new + b * p.kpe_sb : nullptr;
       if (p.fused_new && pw == 0 && qblk == 0 && cur.tile + n == cur.tiles_b) {
         // fused set_mla_kv_buffer (memory_pool.py:880-905): the attention reads the new row from k_new
         const uint4* ks = reinterpret_cast<const uint4*>(knew_row);
         uint4* kd = reinterpret_cast<uint4*>(p.k_buf + loc_b * p.kb_st);
-        for (int i = lane; i < C::ROW_BYTES / 16; i += 32) kd[i] = ks[i];
+        if (kpe_row) {  // set_mla_kv_buffer(layer, loc, k_nope, k_rope): the two parts of the latent row arrive apart
+          const uint4* kr = reinterpret_cast<const uint4*>(kpe_row);
+          for (int i = lane; i < C::Dv * 2 / 16; i += 32) kd[i] = ks[i];
+          if (lane < (C::D - C::Dv) * 2 / 16) kd[C::Dv * 2 / 16 + lane] = kr[lane];
+        } else {
+          for (int i = lane; i < C::ROW_BYTES / 16; i += 32) kd[i] = ks[i];
+        }
       }
       const uint8_t* r2t_row = reinterpret_cast<const uint8_t*>(p.r2t) + (req * p.r2t_stride) * (p.idx64 ? 8 : 4);
       int32_t lo = 0, hi = 0, nlo = 0, nhi = 0;
       auto load_idx = [&](int j, int32_t& dlo, int32_t& dhi) {
         int64_t pos = kv0 + (int64_t)j * C::SUB_T + pw * RW + lane;
         if (pos > kv1 - 1) pos = kv1 - 1;  // tail: duplicate the last valid row (masked by the consumers)
+        pos >>= p.page_shift;              // page tables (cutlass_mla_decode): one entry per page
         if (lane < RW) {
           if (p.idx64) {
             const int2 w = *reinterpret_cast<const int2*>(r2t_row + pos * 8);
@@ -134,6 +142,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_mla_mma_kernel(const _
           }
         }
       };
+      const int64_t page_mask = ((int64_t)1 << p.page_shift) - 1;
       load_idx(0, lo, hi);
       const int nsub = 2 * n;
       for (int j = 0; j < nsub; ++j, ++gs) {
@@ -144,10 +153,21 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_mla_mma_kernel(const _
         if (lane == 0) mbar_arrive_expect_tx(&full[s], RW * C::ROW_BYTES);
         __syncwarp();
         if (lane < RW) {
-          const int64_t idx = p.idx64 ? (((int64_t)hi << 32) | (uint32_t)lo) : (int64_t)lo;
+          int64_t idx = p.idx64 ? (((int64_t)hi << 32) | (uint32_t)lo) : (int64_t)lo;
+          if (p.page_shift) {
+            int64_t pos = kv0 + (int64_t)j * C::SUB_T + pw * RW + lane;
+            if (pos > kv1 - 1) pos = kv1 - 1;
+            idx = (idx << p.page_shift) + (pos & page_mask);
+          }
           const uint16_t* src = p.k_buf + idx * p.kb_st;
-          if (idx == loc_b) src = knew_row;
-          bulk_g2s(smem + s * C::STAGE_BYTES + (pw * RW + lane) * C::ROW_PITCH, src, C::ROW_BYTES, &full[s]);
+          uint8_t* dst = smem + s * C::STAGE_BYTES + (pw * RW + lane) * C::ROW_PITCH;
+          if (idx == loc_b && kpe_row) {  // the new row in two pieces: same transaction bytes
+            bulk_g2s(dst, knew_row, C::Dv * 2, &full[s]);
+            bulk_g2s(dst + C::Dv * 2, kpe_row, (C::D - C::Dv) * 2, &full[s]);
+          } else {
+            if (idx == loc_b) src = knew_row;
+            bulk_g2s(dst, src, C::ROW_BYTES, &full[s]);
+          }
         }
         lo = nlo;
         hi = nhi;
@@ -187,13 +207,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_mla_mma_kernel(const _
     {
       const uint16_t* q0 = p.q + b * p.q_sb + (int64_t)(row0 + g) * p.q_sh + kh * (C::D / 2) + 2 * t;
       const uint16_t* q1 = q0 + 8 * p.q_sh;
+      // q_nope / q_pe given apart (cutlass_mla_backend.py:252-262): columns >= 512 come from q_pe, no concat
+      const uint16_t* e0 = p.q_pe ? p.q_pe + b * p.qpe_sb + (int64_t)(row0 + g) * p.qpe_sh + 2 * t - C::Dv : nullptr;
+      const uint16_t* e1 = e0 ? e0 + 8 * p.qpe_sh : nullptr;
       const bool v0 = g < rows_valid, v1 = g + 8 < rows_valid;
 #pragma unroll
       for (int ks = 0; ks < KH_STEPS; ++ks) {
-        qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16) : 0u;
-        qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16) : 0u;
-        qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 8) : 0u;
-        qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 8) : 0u;
+        const int col = kh * (C::D / 2) + ks * 16;  // 16-column k-steps never straddle column 512
+        const bool pe = p.q_pe != nullptr && col >= C::Dv;
+        const uint16_t* a0 = pe ? e0 + col : q0 + ks * 16;
+        const uint16_t* a1 = pe ? e1 + col : q1 + ks * 16;
+        qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(a0) : 0u;
+        qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(a1) : 0u;
+        qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(a0 + 8) : 0u;
+        qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(a1 + 8) : 0u;
       }
     }
     float o[8][4];

@@ -9,113 +9,19 @@
 // type before it is quantised), so q and the scales are BIT-IDENTICAL to rmsnorm -> per_token_group_quant_fp8 and
 // silu_and_mul -> per_token_group_quant_fp8 (tests/test_gpu_quant_gemm.py checks that).
 #include "common.cuh"
+#include "rmsnorm_row.cuh"
 
 namespace b200 {
 
-// quantise 8 values owned by one of the 16 threads of a 128-group; returns the packed fp8 bytes, writes the scale
-__device__ __forceinline__ uint2 quant_group8(const float (&v)[8], float eps, float fmin_, float fmax_, float* s_out,
-                                              bool write_scale) {
-  float amax = eps;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o, 16));
-  const float ys = __fdiv_rn(amax, fmax_);
-  if (write_scale) *s_out = ys;
-  uint32_t packed[2];
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    uint32_t pk = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float qv = fminf(fmaxf(__fdiv_rn(v[4 * i + j], ys), fmin_), fmax_);
-      pk |= (uint32_t)__nv_cvt_float_to_fp8(qv, __NV_SATFINITE, __NV_E4M3) << (8 * j);
-    }
-    packed[i] = pk;
-  }
-  return make_uint2(packed[0], packed[1]);
-}
-
-// one CTA per token row, 256 threads, thread t owns the 8-element vectors t, t + 256, ... (NV of them): the row
-// stays in registers between the sum of squares and the quantisation.  H % 128 == 0, H <= 256 * 8 * NV.
+// one CTA per token row, 256 threads (rmsnorm_row.cuh)
 template <bool BF16, int NV>
-__global__ void __launch_bounds__(256) rmsnorm_quant_fp8_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ residual,
-                                                                const uint16_t* __restrict__ w, uint16_t* __restrict__ out,
-                                                                uint8_t* __restrict__ q, int64_t q_sm, float* __restrict__ s,
-                                                                int64_t s_sm, int64_t s_sg, int H, float eps, float q_eps,
-                                                                float fmin_, float fmax_) {
+__global__ void __launch_bounds__(256) rmsnorm_quant_fp8_kernel(const uint16_t* __restrict__ x, const RowNormArgs a) {
   griddep_wait();    // programmatic dependent launch: everything below reads what the previous kernel wrote
   griddep_launch();  // the next kernel may take its blocks and run its prologue
   const int64_t m = blockIdx.x;
-  const int nvec = H >> 3;
   __shared__ float red[8];
-  float v[NV][8];
-  float ss = 0.f;
-#pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const int vec = threadIdx.x + j * 256;
-    if (vec < nvec) {
-      const uint4 xr = *reinterpret_cast<const uint4*>(x + m * H + vec * 8);
-      const uint32_t xw[4] = {xr.x, xr.y, xr.z, xr.w};
-      if (residual) {
-        const uint4 rr = *reinterpret_cast<const uint4*>(residual + m * H + vec * 8);
-        const uint32_t rw[4] = {rr.x, rr.y, rr.z, rr.w};
-        uint32_t ow[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 a = unpack_half2<BF16>(xw[i]), b = unpack_half2<BF16>(rw[i]);
-          ow[i] = pack_half2<BF16>(a.x + b.x, a.y + b.y);
-          const float2 f = unpack_half2<BF16>(ow[i]);
-          v[j][2 * i] = f.x;
-          v[j][2 * i + 1] = f.y;
-        }
-        *reinterpret_cast<uint4*>(residual + m * H + vec * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 f = unpack_half2<BF16>(xw[i]);
-          v[j][2 * i] = f.x;
-          v[j][2 * i + 1] = f.y;
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) ss += v[j][i] * v[j][i];
-    }
-  }
-  ss = warp_sum(ss);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
-  __syncthreads();
-  // (b200_rmsnorm runs this same kernel for aligned rows, so the fused and the two-step path share the summation order)
-  ss = 0.f;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) ss += red[i];
-  const float r = rsqrtf(ss / (float)H + eps);
-#pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const int vec = threadIdx.x + j * 256;
-    if (vec < nvec) {
-      const uint4 wr = *reinterpret_cast<const uint4*>(w + vec * 8);
-      const uint32_t ww[4] = {wr.x, wr.y, wr.z, wr.w};
-      float y[8];
-      uint32_t ow[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float2 wf = unpack_half2<BF16>(ww[i]);
-        const float n0 = half_to_float<BF16>(float_to_half<BF16>(v[j][2 * i] * r));
-        const float n1 = half_to_float<BF16>(float_to_half<BF16>(v[j][2 * i + 1] * r));
-        ow[i] = pack_half2<BF16>(n0 * wf.x, n1 * wf.y);
-        const float2 f = unpack_half2<BF16>(ow[i]);
-        y[2 * i] = f.x;
-        y[2 * i + 1] = f.y;
-      }
-      if (out) *reinterpret_cast<uint4*>(out + m * H + vec * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-      if (q) {  // (uniform over the grid; b200_rmsnorm's fast path runs this kernel without the quantiser)
-        const int g = vec >> 4;
-        const uint2 pk = quant_group8(y, q_eps, fmin_, fmax_, s + m * s_sm + g * s_sg, (vec & 15) == 0);
-        *reinterpret_cast<uint2*>(q + m * q_sm + vec * 8) = pk;
-      }
-    }
-  }
+  const uint16_t* xrow = x + m * a.H;
+  rmsnorm_quant_row<BF16, NV>(a, m, [&](int vec) { return *reinterpret_cast<const uint4*>(xrow + vec * 8); }, red);
 }
 
 // x [M, 2d] = (gate | up); one thread per 8 outputs, 16 threads per 128-group.  d % 128 == 0.
@@ -166,10 +72,10 @@ extern "C" int b200_rmsnorm_quant_fp8(const void* x, void* residual, const void*
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "rmsnorm_quant_fp8: requires an sm_100 device (got sm_%d); no fallback", arch);
   cudaStream_t st = (cudaStream_t)stream;
   const int nv = (H / 8 + 255) / 256;
-#define B200_RQ(BF, NV)                                                                                                   \
-  launch_pdl(rmsnorm_quant_fp8_kernel<BF, NV>, dim3(M), dim3(256), 0, st, (const uint16_t*)x, (uint16_t*)residual, (const uint16_t*)weight, \
-                                                      (uint16_t*)out, (uint8_t*)q, q_sm, s, s_sm, s_sg, H, eps, q_eps,   \
-                                                      fp8_min, fp8_max)
+  RowNormArgs ra;
+  ra.residual = (uint16_t*)residual; ra.w = (const uint16_t*)weight; ra.out = (uint16_t*)out; ra.q = (uint8_t*)q; ra.q_sm = q_sm;
+  ra.s = s; ra.s_sm = s_sm; ra.s_sg = s_sg; ra.H = H; ra.eps = eps; ra.q_eps = q_eps; ra.fmin_ = fp8_min; ra.fmax_ = fp8_max;
+#define B200_RQ(BF, NV) launch_pdl(rmsnorm_quant_fp8_kernel<BF, NV>, dim3(M), dim3(256), 0, st, (const uint16_t*)x, ra)
   if (dtype == B200_BF16) {
     if (nv <= 1) B200_RQ(true, 1); else if (nv <= 2) B200_RQ(true, 2); else B200_RQ(true, 4);
   } else {

@@ -293,9 +293,13 @@ def decode_attention_workspace_bytes(B: int, Hq: int, Dv: int, num_splits: int) 
     return load().b200_decode_attn_workspace_size(B, Hq, Dv, num_splits)
 
 
+_INT_META = (torch.int64, torch.int32)
+
+
 def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logits, req_to_token, req_pool_indices,
                      seq_lens, sm_scale: float, logit_cap: float, *, max_seq_len: int = 0, num_splits: int = 0,
-                     fused_kv_write: bool = False, quant_fp8: bool = False, quant_eps: float = 1e-10):
+                     fused_kv_write: bool = False, quant_fp8: bool = False, quant_eps: float = 1e-10,
+                     q_rope: Optional[torch.Tensor] = None, k_rope: Optional[torch.Tensor] = None, page_size: int = 1):
     """Same positional signature as torch.ops.sgl_kernel.decode_attention_cpu (decode.cpp:1375-1388;
     schema torch_extension_cpu.cpp:264-268) on CUDA tensors.
 
@@ -305,6 +309,10 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     MLA is detected like the reference: k_cache and v_cache share storage, Hkv == 1, D == Dv + 64 (:1455).
     fused_kv_write=True moves the append into the attention kernel; it requires that slot loc[b] is referenced
     by request b only (true for SGLang's allocators; schedule_batch.py:1556-1568).
+    seq_lens / req_pool_indices / loc are int64 as decode.cpp:1446-1450 requires, or int32 as the CUDA-graph runner
+    allocates them (cuda_graph_runner.py:273-276); req_pool_indices=None means request b owns row b of the table.
+    MLA extras (cutlass_mla_backend.py:226-285): q_rope [B,Hq,64] with query = q_nope [B,Hq,512]; k_rope [B,1,64] with
+    key = the latent part [B,1,512] (set_mla_kv_buffer); page_size P > 1: req_to_token is a [B, pages] page table.
     quant_fp8=True also returns (x_q, x_s) = per_token_group_quant_fp8(output.view(B, Hq*Dv), 128,
     column_major_scales=True) for the FP8 block o_proj (fp8_utils.py:202-204), bit-identical to the separate call; the
     split-merge kernel emits it where the tuned kernel runs (Dv == 128), otherwise the quantiser is launched here.
@@ -317,6 +325,10 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
         raise RuntimeError("query, k_cache and v_cache must be contiguous in the last dimension")
     B, Hq, D = query.shape
     Hkv, Dv = k_cache.shape[1], v_cache.shape[2]
+    if q_rope is not None:
+        if q_rope.dim() != 3 or q_rope.shape[:2] != query.shape[:2] or q_rope.stride(-1) != 1 or q_rope.dtype != query.dtype:
+            raise RuntimeError("q_rope must be [B, Hq, rope_dim] of query's dtype, contiguous in the last dimension")
+        D = D + q_rope.shape[2]
     if k_cache.shape[2] != D or v_cache.shape[1] != Hkv:
         raise RuntimeError("k_cache / v_cache shapes do not match query")
     if tuple(output.shape) != (B, Hq, Dv) or not output.is_contiguous():
@@ -326,16 +338,21 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     if req_to_token.dtype not in (torch.int32, torch.int64) or req_to_token.stride(1) != 1:
         raise RuntimeError("req_to_token must be int32/int64 with contiguous rows")  # decode.cpp:1441-1445
     for name, t in (("seq_lens", seq_lens), ("req_pool_indices", req_pool_indices)):
-        if t.dtype != torch.int64 or not t.is_contiguous():
-            raise RuntimeError(f"{name} must be a contiguous int64 tensor")  # decode.cpp:1446-1450
-    if seq_lens.numel() != B or req_pool_indices.numel() != B:
-        raise RuntimeError("seq_lens / req_pool_indices must have B entries")
+        if t is None and name == "req_pool_indices":
+            continue
+        if t.dtype not in _INT_META or not t.is_contiguous():
+            raise RuntimeError(f"{name} must be a contiguous int64 (or int32) tensor")  # decode.cpp:1446-1450
+        if t.numel() != B:
+            raise RuntimeError("seq_lens / req_pool_indices must have B entries")
     write_kv = 0
     if key is not None:
-        if loc is None or loc.dtype != torch.int64 or not loc.is_contiguous() or loc.numel() != B:
-            raise RuntimeError("loc must be a contiguous int64 [B] tensor")
+        if loc is None or loc.dtype not in _INT_META or not loc.is_contiguous() or loc.numel() != B:
+            raise RuntimeError("loc must be a contiguous int64 (or int32) [B] tensor")
         if key.stride(-1) != 1 or (value is not None and value.stride(-1) != 1):
             raise RuntimeError("key and value must be contiguous in the last dimension")
+        if k_rope is not None and (k_rope.stride(-1) != 1 or k_rope.numel() != B * k_rope.shape[-1]
+                                   or key.shape[-1] + k_rope.shape[-1] != D):
+            raise RuntimeError("k_rope must be [B, 1, rope_dim] with key holding the other D - rope_dim columns")
         write_kv = 2 if fused_kv_write else 1
     lib = load()
     p = _lib.DecodeAttnParams()
@@ -350,7 +367,16 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     p.out = output.data_ptr()
     p.req_to_token, p.req_to_token_stride = req_to_token.data_ptr(), req_to_token.stride(0)
     p.idx_is_i64 = int(req_to_token.dtype == torch.int64)
-    p.req_pool_indices, p.seq_lens = req_pool_indices.data_ptr(), seq_lens.data_ptr()
+    p.req_pool_indices = req_pool_indices.data_ptr() if req_pool_indices is not None else None
+    p.seq_lens = seq_lens.data_ptr()
+    p.meta_i32_mask = (int(seq_lens.dtype == torch.int32)
+                       | (int(req_pool_indices is not None and req_pool_indices.dtype == torch.int32) << 1)
+                       | (int(key is not None and loc.dtype == torch.int32) << 2))
+    p.page_size = int(page_size)
+    if q_rope is not None:
+        p.q_rope, p.qrope_stride_b, p.qrope_stride_h = q_rope.data_ptr(), q_rope.stride(0), q_rope.stride(1)
+    if key is not None and k_rope is not None:
+        p.k_rope_new, p.krope_stride_b = k_rope.data_ptr(), k_rope.stride(0)
     p.B, p.Hq, p.Hkv, p.D, p.Dv = B, Hq, Hkv, D, Dv
     p.dtype = DTYPE_CODE[query.dtype]
     p.write_kv = write_kv
@@ -377,6 +403,53 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
         else:
             check(rc)
     return output, x_q, x_s
+
+
+def cutlass_mla_get_workspace_size(max_seq_len: int, num_batches: int, sm_count: int = 0, num_kv_splits: int = 1) -> int:
+    """sgl_kernel.cutlass_mla_get_workspace_size (sgl-kernel/python/sgl_kernel/attention.py:128-138;
+    cutlass_mla_kernel.cu:248-266).  The tuned kernel's scratch does not grow with the batch or the context."""
+    assert max_seq_len > 0, f"max_seq_len must be greater than 0, got {max_seq_len}"
+    assert num_batches > 0, f"num_batches must be greater than 0, got {num_batches}"
+    return int(load().b200_decode_attn_workspace_size(num_batches, 128, 512, 1))
+
+
+def cutlass_mla_decode(q_nope: torch.Tensor, q_pe: torch.Tensor, kv_c_and_k_pe_cache: torch.Tensor, seq_lens: torch.Tensor,
+                       page_table: torch.Tensor, workspace: torch.Tensor, sm_scale: float, num_kv_splits: int = 1) -> torch.Tensor:
+    """sgl_kernel.cutlass_mla_decode (sgl-kernel/python/sgl_kernel/attention.py:54-125 ->
+    csrc/attention/cutlass_mla_kernel.cu:210-246): MLA absorbed decode over a paged latent cache.
+
+    q_nope [B,H,512], q_pe [B,H,64] (any batch/head strides), kv_c_and_k_pe_cache [pages, P, 576], seq_lens int32 [B],
+    page_table int32 [B, blocks] of page ids -> [B, H, 512].  Same asserts as the reference wrapper; no padding of H to
+    128 (the kernel works on 16-head blocks) and no concatenation of q_nope / q_pe (two pointers)."""
+    assert q_nope.ndim == 3, f"q_nope must be a 3D tensor, but got {q_nope.ndim}"
+    assert q_pe.ndim == 3, f"q_pe must be a 3D tensor, but got {q_pe.ndim}"
+    assert kv_c_and_k_pe_cache.ndim == 3, f"kv_c_and_k_pe_cache must be a 3D tensor, but got {kv_c_and_k_pe_cache.ndim}"
+    B_q, H, D_q_nope = q_nope.shape
+    B_q_2, H_2, D_q_pe = q_pe.shape
+    assert (B_q == B_q_2) and (H == H_2)
+    _, PAGE_SIZE, D_ckv = kv_c_and_k_pe_cache.shape
+    assert D_q_nope == 512 and D_q_pe == 64 and D_ckv == 576
+    assert H <= 128, f"H must be <= 128, but got {H}"
+    assert len(page_table.shape) == 2
+    B_block_table, block_num = page_table.shape
+    assert B_block_table == B_q
+    assert block_num > 0, f"block num must be greater than 0, got {block_num}"
+    assert block_num % (128 / PAGE_SIZE) == 0
+    assert q_nope.dtype in (torch.float16, torch.bfloat16), f"q_nope.dtype needs to be fp16 or bf16 but got {q_nope.dtype}."
+    assert q_nope.dtype == q_pe.dtype == kv_c_and_k_pe_cache.dtype
+    assert seq_lens.dtype == torch.int32, f"seq_lens.dtype needs to be int32 but got {seq_lens.dtype}."
+    assert page_table.dtype == torch.int32, f"page_table.dtype needs to be int32 but got {page_table.dtype}."
+    if PAGE_SIZE & (PAGE_SIZE - 1):
+        raise NotImplementedError("cutlass_mla_decode: page size must be a power of two")
+    out = q_nope.new_empty((B_q, H, 512))
+    if not kv_c_and_k_pe_cache.is_contiguous():
+        raise RuntimeError("kv_c_and_k_pe_cache must be contiguous")
+    rows = kv_c_and_k_pe_cache.view(-1, 1, 576)
+    if page_table.stride(1) != 1:
+        page_table = page_table.contiguous()
+    decode_attention(q_nope, rows, rows[:, :, :512], out, None, None, None, workspace, page_table, None,
+                     seq_lens.contiguous(), sm_scale, 0.0, q_rope=q_pe, page_size=PAGE_SIZE)
+    return out
 
 
 def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices, seq_lens,

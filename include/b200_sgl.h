@@ -40,7 +40,7 @@ extern "C" {
 #define B200_F16 1
 #define B200_F32 2
 
-#define B200_SGL_ABI_VERSION 1
+#define B200_SGL_ABI_VERSION 2
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -81,9 +81,10 @@ typedef struct b200_decode_attn_params {
   void* out;                /* [B, Hq, Dv] contiguous */
   const void* req_to_token; /* [max_reqs, max_context_len] int32 or int64 */
   int64_t req_to_token_stride;
-  const int64_t* req_pool_indices; /* [B] */
-  const int64_t* seq_lens;         /* [B] includes the token being decoded */
-  const int64_t* out_cache_loc;    /* [B] */
+  const void* req_pool_indices;    /* [B] int64 (schedule_batch.py:1138) or int32 (cuda_graph_runner.py:273-276, see
+                                      meta_i32_mask); NULL = identity (row b of the table belongs to request b) */
+  const void* seq_lens;            /* [B] int64 or int32; includes the token being decoded */
+  const void* out_cache_loc;       /* [B] int64 or int32 */
   void* workspace;          /* >= b200_decode_attn_workspace_size(...) bytes, 16-byte aligned */
   size_t workspace_bytes;
   int32_t idx_is_i64;
@@ -94,6 +95,20 @@ typedef struct b200_decode_attn_params {
   int32_t max_seq_len;      /* host-side upper bound of seq_lens (e.g. seq_lens_cpu.max()); 0 = unknown */
   float sm_scale;
   float logit_cap;          /* 0 = off */
+  /* --- ABI version 2 --- */
+  int32_t meta_i32_mask;    /* bit 0: seq_lens is int32, bit 1: req_pool_indices is int32, bit 2: out_cache_loc is int32 */
+  int32_t page_size;        /* <= 1: `req_to_token` holds token slots.  A power of two P > 1: it is a page table
+                               (create_flashmla_kv_indices_triton, utils.py:44-94; cutlass_mla_decode's `page_table`)
+                               and token t of request b lives in row table[b, t / P] * P + t % P of k_buf.
+                               MLA and the generic kernel only. */
+  /* MLA with the rope parts given apart, as cutlass_mla_backend.py:226-285 / cutlass_mla_decode
+   * (sgl-kernel/python/sgl_kernel/attention.py:54-125) pass them: q = q_nope [B, Hq, 512] and q_rope [B, Hq, 64];
+   * k_new = the 512 latent columns of the new row and k_rope_new [B, 64] its rope part (set_mla_kv_buffer,
+   * memory_pool.py:859-876).  NULL = q / k_new hold all 576 columns. */
+  const void* q_rope;
+  int64_t qrope_stride_b, qrope_stride_h;
+  const void* k_rope_new;
+  int64_t krope_stride_b;
 } b200_decode_attn_params;
 
 /* number of KV splits the kernel will use for this problem (so that the caller can size scratch) */
@@ -242,21 +257,44 @@ int b200_rope_neox(void* q, int64_t q_stride_m, void* k, int64_t k_stride_m, con
                    int Hq, int Hkv, int D, float theta, void* stream);
 
 /* --------------------------------------------------------------------------------------------
- * One-shot all-reduce(sum) over NVLink peer memory for the row-parallel linears' outputs.
+ * All-reduce(sum) over NVLink peer memory / NVSwitch multicast for the row-parallel linears' outputs, optionally
+ * fused with the residual-add + RMSNorm (+ FP8 quantisation) that follows it.
  * Replaces the custom P2P all-reduce of sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:203-456 /
  * python/sglang/srt/distributed/device_communicators/custom_all_reduce.py:148,414-480 (call site
- * communication_op.py:11-13).  One process per GPU: every rank allocates a region (b200_ar_alloc), the 64-byte
- * CUDA-IPC handles are exchanged by the host (torch.distributed all_gather), b200_ar_init opens the peers'.
- * b200_ar_allreduce launches ONE kernel on `stream` (no host sync, CUDA-graph capturable); every rank must call
- * it with the same n_elems in the same order.  Results are bit-identical on all ranks (sum in rank order, fp32).
- * b200_ar_error returns 1 if a peer never arrived (the kernel gave up after ~20 s instead of hanging).
+ * communication_op.py:11-13) and the fusion hook python/sglang/srt/layers/flashinfer_comm_fusion.py:122
+ * (flashinfer_allreduce_add_rmsnorm).  One process per GPU.  Two ways to set up:
+ *   (a) b200_ar_alloc on every rank, exchange the 64-byte CUDA-IPC handles on the host (torch.distributed
+ *       all_gather), b200_ar_init opens the peers' regions;
+ *   (b) the host already has peer mappings of a symmetric allocation of b200_ar_region_bytes() zero-filled bytes
+ *       (torch.distributed._symmetric_memory rendezvous): b200_ar_init_ptrs takes the W device pointers and the
+ *       multicast address of the same buffer (0 if the fabric has none), which enables the NVLS kernel.
+ * Every call launches ONE kernel on `stream` (no host sync, CUDA-graph capturable); every rank must make the same
+ * calls with the same sizes in the same order.  Results are identical on all ranks; without multicast they are the
+ * fp32 sum in rank order rounded once.  b200_ar_error returns 1 if a peer never arrived (the kernel gave up after
+ * ~20 s instead of hanging).
  * ------------------------------------------------------------------------------------------ */
 size_t b200_ar_region_bytes(size_t max_message_bytes);
 int b200_ar_alloc(size_t max_message_bytes, void** region_out, void* ipc_handle_out64);
+void b200_ar_free_region(void* region); /* a region from b200_ar_alloc that never reached b200_ar_init */
 int b200_ar_init(void* own_region, const void* handles, int rank, int world, size_t max_message_bytes, void** ctx_out);
+int b200_ar_init_ptrs(const uint64_t* regions /* host array [world] of device pointers */, uint64_t multicast, int rank,
+                      int world, size_t max_message_bytes, void** ctx_out);
+int b200_ar_has_multicast(void* ctx);
 int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int dtype, void* stream);
-/* 1 = one-shot kernel, 2 = two-shot kernel, 0 = ncclAllReduce is faster for this (world, message size) */
+/* in [M, H] (this rank's partial sums); residual [M, H] += sum (stored back); y = RMSNorm(residual) * weight;
+ * norm_out [M, H] = y (may be NULL); q / s = per_token_group_quant_fp8(y, 128) with the strides of
+ * b200_per_token_group_quant_fp8 (may be NULL).  Equal, bit for bit when no multicast is involved, to
+ * b200_ar_allreduce followed by b200_rmsnorm_quant_fp8.  H % 128 == 0, H <= 8192.  B200_ERR_UNSUPPORTED when the
+ * message is better served by the two separate kernels (large message, many ranks, no multicast). */
+int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* residual, const void* weight, void* norm_out, void* q,
+                                  int64_t q_stride_m, float* s, int64_t s_stride_m, int64_t s_stride_g, int M, int H,
+                                  int dtype, float eps, float quant_eps, float fp8_min, float fp8_max, void* stream);
+/* measured policy: 1 = one-shot kernel, 2 = two-shot kernel, 3 = NVLS multicast kernel, 4 = row-layout one-shot,
+ * 0 = ncclAllReduce is faster for this (world, message size).  b200_ar_mode = b200_ar_mode2 without multicast. */
 int b200_ar_mode(int world, size_t bytes);
+int b200_ar_mode2(int world, size_t bytes, int has_multicast);
+/* force a kernel for every following call (-1 = back to the policy); must be the same on every rank */
+int b200_ar_set_mode(void* ctx, int mode);
 int b200_ar_error(void* ctx);
 void b200_ar_destroy(void* ctx);
 

@@ -90,9 +90,11 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     if attn_logits is not None:
         assert attn_logits.dtype == torch.float32 and attn_logits.is_contiguous()
         num_kv_splits = attn_logits.shape[2]
-    loc64, rpi, sl = _as_i64(loc), _as_i64(req_pool_indices), _as_i64(seq_lens)
     if key is None:
         write_kv = False
+    loc64 = _as_i64(loc) if loc is not None else None
+    assert loc64 is not None or not write_kv
+    rpi, sl = _as_i64(req_pool_indices), _as_i64(seq_lens)
     rc = lib().orc_decode_attention(
         _p(query), _i64(query.stride(0)), _i64(query.stride(1)),
         _p(k_cache), _i64(k_cache.stride(0)), _i64(k_cache.stride(1)),

@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(256) group_quant_fp8_kernel(const uint16_t* __
 #pragma unroll
   for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
 #pragma unroll
-  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o, 16));
+  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffu << (threadIdx.x & 16), amax, o, 16));
   const float ys = __fdiv_rn(amax, fmax_);
   if (sub == 0) s[m * s_sm + g * s_sg] = ys;
   uint32_t packed[2];

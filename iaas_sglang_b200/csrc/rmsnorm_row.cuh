@@ -14,8 +14,10 @@ __device__ __forceinline__ uint2 quant_group8(const float (&v)[8], float eps, fl
   float amax = eps;
 #pragma unroll
   for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+  // only the 16 lanes of this group are named: the other half of the warp may have left (H or M*d an odd multiple of 128)
+  const unsigned half_mask = 0xffffu << (threadIdx.x & 16);
 #pragma unroll
-  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o, 16));
+  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(half_mask, amax, o, 16));
   const float ys = __fdiv_rn(amax, fmax_);
   if (write_scale) *s_out = ys;
   uint32_t packed[2];

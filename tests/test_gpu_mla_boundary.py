@@ -91,7 +91,7 @@ def _mla_plugin(B, Hq, ctx, lens, meta_dtype=torch.int64):
     from tests.test_gpu_backend import make_runner
 
     runner, backend = make_runner(B, Hq, 1, 576, ctx, layers=1, mla=True)
-    c = DecodeCase(B, Hq, 1, 576, 512, lens, max_ctx=ctx, extra_reqs=2)
+    c = DecodeCase(B, Hq, 1, 576, 512, lens, max_ctx=ctx, extra_reqs=3)
     pool, r2t = runner.token_to_kv_pool, runner.req_to_token_pool
     r2t.req_to_token.copy_(c.req_to_token)
     T = c.k_buf.shape[0]

@@ -72,6 +72,8 @@ SIGNATURES = {
     "b200_sm_arch": (c_int, []),
     "b200_sm_count": (c_int, []),
     "b200_launch_count": (C.c_ulonglong, []),
+    "b200_tune_set": (c_int, [C.c_char_p, c_int]),
+    "b200_tune_get": (c_int, [C.c_char_p, C.POINTER(c_int)]),
     "b200_decode_attn_num_splits": (c_int, [c_int] * 7),
     "b200_decode_attn_workspace_size": (c_size_t, [c_int] * 4),
     "b200_decode_attn": (c_int, [C.POINTER(DecodeAttnParams), c_void_p]),
@@ -145,6 +147,17 @@ def load() -> C.CDLL:
         raise ImportError("libb200sgl.so ABI version mismatch")
     _lib = lib
     return lib
+
+
+def tune_set(name: str, value: int) -> None:
+    """Developer / tuning knob (csrc/runtime.cu kTune); the environment (B200_*) is read once at load."""
+    check(load().b200_tune_set(name.encode(), int(value)))
+
+
+def tune_get(name: str) -> int:
+    v = c_int(0)
+    check(load().b200_tune_get(name.encode(), C.byref(v)))
+    return v.value
 
 
 def last_error() -> str:

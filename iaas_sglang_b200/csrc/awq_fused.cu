@@ -449,9 +449,7 @@ static int aq_cluster_capacity(int S) {
 static AwqPlan aq_plan(int M, int N, int K, int mt_pad) {
   const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
   const int sub = N / AQ_BN, kb = K / 64;
-  static int force_nt = -1, force_s = -1;
-  if (force_nt < 0) { const char* e = getenv("B200_AWQ_NT"); force_nt = e ? atoi(e) : 0; }
-  if (force_s < 0) { const char* e = getenv("B200_AWQ_SPLITS"); force_s = e ? atoi(e) : 0; }
+  const int force_nt = tune(TUNE_AWQ_NT), force_s = tune(TUNE_AWQ_SPLITS);
   AwqPlan best{1, 1, 2, 0};
   double best_cost = 1e30;
   const int nt_max = mt_pad <= 128 ? 3 : (mt_pad <= 256 ? 2 : 1);  // NT * accumulator columns <= 512
@@ -540,8 +538,7 @@ int launch_awq_fused(const void* x, int64_t ldx, const int32_t* qweight, const v
   ap.stages = pl.stages;
   ap.n_tiles = (N / AQ_BN + pl.nt - 1) / pl.nt;
   {
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("B200_AWQ_DEBUG"); dbg = e ? atoi(e) : 0; }
+    const int dbg = tune(TUNE_AWQ_DEBUG);
     if (dbg & 1)
       fprintf(stderr, "[awq_fused] M=%d N=%d K=%d NT=%d S=%d tiles=%d stages=%d smem=%d\n", M, N, K, pl.nt, pl.splits, ap.n_tiles, pl.stages, pl.smem);
   }

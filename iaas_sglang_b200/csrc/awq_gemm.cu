@@ -79,8 +79,7 @@ extern "C" int b200_awq_w4a16_mm(const void* x, int64_t ldx, const int32_t* qwei
   cudaStream_t st = (cudaStream_t)stream;
   if (awq_fused_shape(M, N, K) && group % 8 == 0 && ldx % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)qweight & 15) == 0 &&
       ((uintptr_t)scales & 15) == 0) {
-    static int use_v2 = -1;
-    if (use_v2 < 0) { const char* e = getenv("B200_AWQ_V1"); use_v2 = (e && atoi(e)) ? 0 : 1; }
+    const bool use_v2 = tune(TUNE_AWQ_V1) == 0;
     if (use_v2 && awq_fused_applicable(M, N, K, group))
       return launch_awq_fused(x, ldx, qweight, scales, qzeros, bias, out, ldo, dtype, M, N, K, group, st);
     SkinnyParams sp{};

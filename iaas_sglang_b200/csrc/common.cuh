@@ -23,6 +23,13 @@ int device_sm_count();
 // programmatic dependent launch (B200_PDL=0 disables): kernels that support it are launched with
 // cudaLaunchAttributeProgrammaticStreamSerialization and order themselves with griddepcontrol.wait
 bool pdl_enabled();
+// Tuning / developer knobs: read from the environment ONCE when the library is loaded (never on a launch path);
+// b200_tune_set / b200_tune_get change them at run time (tools/, tests).
+enum TuneKey {
+  TUNE_PDL = 0, TUNE_SK_MAX_M, TUNE_SK_STAGES, TUNE_SK_SPLITS, TUNE_SK_DEBUG, TUNE_GB_PAIR, TUNE_GB_BN, TUNE_GB_PROF,
+  TUNE_AWQ_NT, TUNE_AWQ_SPLITS, TUNE_AWQ_DEBUG, TUNE_AWQ_V1, TUNE_ATTN_BULK_MIN, TUNE_GB_EPI, TUNE_COUNT
+};
+int tune(TuneKey k);
 
 #ifdef __CUDACC__
 // Launch `kern` as a programmatic dependent of the previous kernel of the stream (plain launch with B200_PDL=0).

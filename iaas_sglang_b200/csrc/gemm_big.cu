@@ -444,9 +444,9 @@ static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = PAIR > 1 ? 1 : 0;
-  static int prof = -1;
+  const int prof = tune(TUNE_GB_PROF);
   static long long* dprof = nullptr;
-  if (prof < 0) { const char* e = getenv("B200_GB_PROF"); prof = e ? atoi(e) : 0; if (prof) cudaMalloc(&dprof, 160 * 64); }
+  if (prof && !dprof) cudaMalloc(&dprof, 160 * 64);
   bp.prof = prof ? dprof : nullptr;
   B200_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, bp, stages));
   if (prof) {
@@ -474,10 +474,7 @@ int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw,
   bp.sb = sb; bp.sb_sk = sb_sk; bp.sb_sn = sb_sn;
   bp.bias = bias; bp.out = out; bp.ldo = ldo; bp.out_bf16 = out_bf16;
   bp.M = M; bp.N = N; bp.K = K;
-  static int pair = -1;
-  if (pair < 0) { const char* e = getenv("B200_GB_PAIR"); pair = e ? atoi(e) : 2; }
-  static int bn = -1;
-  if (bn < 0) { const char* e = getenv("B200_GB_BN"); bn = e ? atoi(e) : 128; }
+  const int pair = tune(TUNE_GB_PAIR), bn = tune(TUNE_GB_BN);
   if (mode == 0) {
     // fp8: the per-k-block TMEM hand-shake with remote CTAs is too slow for pairs (464 vs 1190 TFLOP/s measured).
     // 128-wide tiles have four TMEM buffers, so the tensor core never waits for the promotion (the MMA thread is then

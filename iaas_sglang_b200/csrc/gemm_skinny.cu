@@ -515,18 +515,12 @@ size_t skinny_workspace_bytes(int, int, int) { return 2048 * 8 * 8; }  // (devel
 
 bool skinny_applicable(int M) { return M <= 256; }
 
-// FP8 block-scaled crossover to the persistent large-M kernel.  Measured (tools/kb_cross.py, B200_SK_MAX_M=64 vs 256):
-// at M = 256 the large-M kernel is 1.4-3.4x faster on every cfg 2/4 TP shape (e.g. N 7168 K 4096: 50.2 -> 22.1 us),
-// at M = 128 the skinny kernel still wins 6 of 8 shapes.  The default stays 256 until the GPU parity suite has run
-// with 128 (B200_SK_MAX_M=128 selects it today); next round's first change.
+// FP8 block-scaled crossover to the persistent large-M kernel (knob sk_max_m, default 128).  Measured
+// (tools/kb_cross.py): at M = 256 the large-M kernel is 1.4-3.4x faster on every cfg 2/4 TP shape (N 7168 K 4096:
+// 50.2 -> 22.1 us); at M <= 128 the skinny kernel wins.
 bool skinny_applicable_fp8(int M) {
-  static int max_m = -1;
-  if (max_m < 0) {
-    const char* e = getenv("B200_SK_MAX_M");
-    max_m = e ? atoi(e) : 256;
-    if (max_m > 256) max_m = 256;
-  }
-  return M <= max_m;
+  const int max_m = tune(TUNE_SK_MAX_M);
+  return M <= (max_m > 256 ? 256 : max_m);
 }
 
 struct SkinnyPlan {
@@ -544,11 +538,7 @@ static SkinnyPlan skinny_plan(int mode, int mt_pad) {
   pl.tab_cap = mode == 0 ? tab_bytes / (mt_pad * 4) : 0;
   int stages = (budget - SK_FIXED_SMEM - tab_bytes) / stage_bytes;
   if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
-  {
-    static int cap = -1;
-    if (cap < 0) { const char* e = getenv("B200_SK_STAGES"); cap = e ? atoi(e) : 0; }
-    if (cap > 0 && stages > cap) stages = cap;
-  }
+  if (const int cap = tune(TUNE_SK_STAGES); cap > 0 && stages > cap) stages = cap;
   pl.stages = stages;
   pl.smem = stages * stage_bytes + SK_FIXED_SMEM + tab_bytes;
   return pl;
@@ -602,8 +592,7 @@ static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, SkinnyP
       best = sp.n_tiles * s2;
     }
   }
-  static int force = -1;
-  if (force < 0) { const char* e = getenv("B200_SK_SPLITS"); force = e ? atoi(e) : 0; }
+  const int force = tune(TUNE_SK_SPLITS);
   if (force > 0 && force <= SK_MAX_SPLITS && sp.kb_total >= force) S = force;
   sp.splits = S;
   cfg.gridDim = dim3(sp.n_tiles, S);
@@ -656,8 +645,7 @@ int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, Skinny
   sp.stages = pl.stages;
   sp.tab_cap = pl.tab_cap;
   {
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("B200_SK_DEBUG"); dbg = e ? atoi(e) : 0; }
+    const int dbg = tune(TUNE_SK_DEBUG);
     sp.debug = dbg;
     if ((dbg & 256) && workspace && workspace_bytes >= (size_t)sp.n_tiles * 8 * 64) sp.stamps = (unsigned long long*)workspace;
   }

@@ -31,14 +31,33 @@ int launched(const char* what) {
 }
 unsigned long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
-bool pdl_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("B200_PDL");
-    v = (e && e[0] == '0') ? 0 : 1;
+struct TuneEntry { const char* name; const char* env; int def; };
+static const TuneEntry kTune[TUNE_COUNT] = {
+    {"pdl", "B200_PDL", 1},               // programmatic dependent launch between the kernels of a step
+    {"sk_max_m", "B200_SK_MAX_M", 128},   // FP8: largest M served by the skinny (decode) kernel
+    {"sk_stages", "B200_SK_STAGES", 0},   // cap on the skinny kernel's TMA ring depth (0 = as many as fit)
+    {"sk_splits", "B200_SK_SPLITS", 0},   // force the split-K cluster size (0 = heuristic)
+    {"sk_debug", "B200_SK_DEBUG", 0},
+    {"gb_pair", "B200_GB_PAIR", 2},       // large-M kernel: 2 = cta_group::2 pairs where M allows
+    {"gb_bn", "B200_GB_BN", 128},
+    {"gb_prof", "B200_GB_PROF", 0},
+    {"awq_nt", "B200_AWQ_NT", 0},
+    {"awq_splits", "B200_AWQ_SPLITS", 0},
+    {"awq_debug", "B200_AWQ_DEBUG", 0},
+    {"awq_v1", "B200_AWQ_V1", 0},
+    {"attn_bulk_min", "B200_ATTN_BULK_MIN", 0},
+    {"gb_epi", "B200_GB_EPI", 0},
+};
+static int g_tune[TUNE_COUNT];
+static const bool g_tune_loaded = [] {
+  for (int i = 0; i < TUNE_COUNT; ++i) {
+    const char* e = getenv(kTune[i].env);
+    g_tune[i] = e ? atoi(e) : kTune[i].def;
   }
-  return v == 1;
-}
+  return true;
+}();
+int tune(TuneKey k) { return g_tune[k]; }
+bool pdl_enabled() { return g_tune[TUNE_PDL] != 0; }
 
 int device_sm_count() {
   static int cached[64] = {0};
@@ -105,6 +124,19 @@ extern "C" int b200_sm_arch(void) {
   const int arch = major * 10 + minor;
   if (dev >= 0 && dev < 64) cached[dev] = arch;
   return arch;
+}
+
+extern "C" int b200_tune_set(const char* name, int value) {
+  for (int i = 0; i < b200::TUNE_COUNT; ++i)
+    if (name && strcmp(name, b200::kTune[i].name) == 0) { b200::g_tune[i] = value; return B200_OK; }
+  b200::set_error("b200_tune_set: unknown knob '%s'", name ? name : "(null)");
+  return B200_ERR_ARG;
+}
+extern "C" int b200_tune_get(const char* name, int* value) {
+  for (int i = 0; i < b200::TUNE_COUNT; ++i)
+    if (name && value && strcmp(name, b200::kTune[i].name) == 0) { *value = b200::g_tune[i]; return B200_OK; }
+  b200::set_error("b200_tune_get: unknown knob '%s'", name ? name : "(null)");
+  return B200_ERR_ARG;
 }
 
 extern "C" int b200_sm_count(void) { return b200::device_sm_count(); }

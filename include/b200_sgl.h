@@ -49,6 +49,11 @@ int b200_sm_arch(void);
 int b200_sm_count(void);
 /* number of kernels this library has launched (or captured into a CUDA graph) in this process */
 unsigned long long b200_launch_count(void);
+/* Tuning / developer knobs ("pdl", "sk_max_m", "sk_splits", "gb_pair", ...; csrc/runtime.cu lists them with their
+ * B200_* environment names).  The environment is read once when the library is loaded -- never on a launch path;
+ * these two change / read a knob at run time (tools, tests).  No reference counterpart. */
+int b200_tune_set(const char* name, int value);
+int b200_tune_get(const char* name, int* value);
 
 /* --------------------------------------------------------------------------------------------
  * Decode attention over the paged KV pool.

@@ -52,6 +52,32 @@ def test_fp8_blockwise_against_oracle(M, N, K, dist):
     assert rel_l2(out, ref) < 1e-3  # in practice: fp32 promotion per 128-block, bf16 output rounding only
 
 
+# the TP-local shapes of SURVEY 8a row a11 at the decode batch sizes where the skinny / large-M crossover sits:
+# cfg 4 (Llama-70B TP8), cfg 5 (DeepSeek TP8), cfg 2 under TP4, cfg 2's gate_up
+TP_SHAPES = ([(m, n, k) for m in (129, 192, 256) for n, k in [(1280, 8192), (8192, 1024), (7168, 8192), (8192, 3584)]]
+             + [(256, n, k) for n, k in [(2112, 7168), (3072, 1536), (7168, 2048), (4608, 7168), (7168, 2304)]]
+             + [(256, n, k) for n, k in [(1536, 4096), (4096, 1024), (7168, 4096), (4096, 3584)]]
+             + [(64, 28672, 4096), (128, 7168, 8192), (100, 2112, 7168)])
+
+
+@pytest.mark.parametrize("M,N,K", TP_SHAPES)
+def test_fp8_blockwise_tp_shapes_on_both_kernels(M, N, K):
+    """Both FP8 kernels must be right on every shape either side of the crossover (knob sk_max_m): the measured
+    policy may move it."""
+    from iaas_sglang_b200 import _lib
+
+    a, b, sa, sb = make_fp8_gemm_case(M, N, K, seed=M + N + K, dist="realistic")
+    ref = orc.fp8_blockwise_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    old = _lib.tune_get("sk_max_m")
+    try:
+        for kernel, max_m in (("skinny", 256), ("large", 0), ("policy", old)):
+            _lib.tune_set("sk_max_m", max_m)
+            out = _run_fp8(a, b, sa, sb)
+            assert rel_l2(out, ref) < 1e-3, (kernel, rel_l2(out, ref))
+    finally:
+        _lib.tune_set("sk_max_m", old)
+
+
 def test_fp8_blockwise_fp16_out_and_preconditions():
     from iaas_sglang_b200 import ops
 

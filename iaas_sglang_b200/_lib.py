@@ -13,7 +13,7 @@ from typing import Optional
 import torch
 
 _CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
-SO_PATH = os.path.join(_CSRC, "libb200sgl.so")
+SO_PATH = os.environ.get("B200_SGL_LIB") or os.path.join(_CSRC, "libb200sgl.so")   # (override: developer probe builds)
 
 B200_OK, B200_ERR_ARG, B200_ERR_UNSUPPORTED, B200_ERR_CUDA = 0, -1, -2, -3
 BF16, F16, F32 = 0, 1, 2

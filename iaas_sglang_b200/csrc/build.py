@@ -36,8 +36,11 @@ def up_to_date() -> bool:
     return all(os.path.getmtime(d) <= t for d in deps)
 
 
-def _compile(src: str, verbose: bool):
+def _compile(src: str, verbose: bool, force: bool = False):
     obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
+    deps = [os.path.join(HERE, src), os.path.abspath(__file__)] + [h if os.path.isabs(h) else os.path.join(HERE, h) for h in HEADERS]
+    if not force and not verbose and os.path.exists(obj) and all(os.path.getmtime(d) <= os.path.getmtime(obj) for d in deps):
+        return src, obj, 0, ""   # incremental: this object is newer than its source and every header
     cmd = [NVCC, *FLAGS, "-c", os.path.join(HERE, src), "-o", obj]
     if verbose:
         cmd += ["-Xptxas", "-v"]
@@ -61,15 +64,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
         try:
             if not force and up_to_date():   # another process built it while we waited
                 return SO
-            return _build_locked(verbose)
+            return _build_locked(verbose, force)
         finally:
             fcntl.flock(lock, fcntl.LOCK_UN)
 
 
-def _build_locked(verbose: bool) -> str:
+def _build_locked(verbose: bool, force: bool = False) -> str:
     t0 = time.time()
     with ThreadPoolExecutor(max_workers=8) as ex:
-        results = list(ex.map(lambda s: _compile(s, verbose), sources()))
+        results = list(ex.map(lambda s: _compile(s, verbose, force), sources()))
     objs = []
     for src, obj, rc, out in results:
         if verbose or rc != 0:

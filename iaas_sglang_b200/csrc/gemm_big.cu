@@ -24,6 +24,10 @@
 
 #include "common.cuh"
 
+#ifndef GB_PROBE
+#define GB_PROBE 0   // developer probe builds (tools/build_probe.sh): 2 no tcgen05.ld, 4 no FFMA2, 8 release before the loads
+#endif
+
 namespace b200 {
 
 constexpr int GB_BM = 128;   // rows of A per CTA
@@ -182,7 +186,11 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   uint64_t* tempty = tfull + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 4);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // (the shuffle makes the warp index provably warp-uniform for the compiler: the service roles below then keep their
+  // loop state, barrier addresses and UMMA / TMA descriptors in UNIFORM registers.  A role entered through a per-thread
+  // `lane == 0` branch makes ptxas wrap every UTCQMMA / UTCBAR / UTMALDG in an ELECT + R2UR.BROADCAST loop -- about
+  // twenty extra instructions per tensor-core instruction on the one thread that feeds the tensor core.)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int rank = PAIR == 2 ? (int)gb_cluster_rank() : 0;
   const int worker = blockIdx.x / PAIR;
   const bool leader = rank == 0;
@@ -210,8 +218,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
 
   if (warp >= EW) {
     gb_setmaxnreg_dec<SVC_REGS>();
-    if (warp == EW + 2 && lane == 0) {
-      // ================================ TMA producer ================================
+    if (warp == EW + 2) {
+      // ================================ TMA producer (whole warp in the loop, one elected lane issues) ============
       const uint32_t full0_cluster = PAIR == 2 ? gb_mapa(smem_u32(&full[0]), 0) : 0;
       int s = 0;
       uint32_t ph = 0;
@@ -221,23 +229,26 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         const int m0 = (tm * PAIR + rank) * GB_BM, n0 = tn * GB_BN + rank * B_ROWS;
         for (int kb = 0; kb < p.kb_total; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
-          uint8_t* st = smem + s * STAGE_BYTES;
-          if constexpr (PAIR == 1) {
-            mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
-            tma_load_2d(st, &tma_a, kb * GB_BK, m0, &full[s]);
-            tma_load_2d(st + A_BYTES, &tma_b, kb * GB_BK, n0, &full[s]);
-          } else {
-            // both CTAs' copies complete on the LEADER's barrier (it expects the bytes of the pair)
-            if (leader) mbar_arrive_expect_tx(&full[s], 2 * STAGE_BYTES);
-            const uint32_t bar = full0_cluster + (uint32_t)(s * 8);
-            gb_tma_load_2d_pair(st, &tma_a, kb * GB_BK, m0, bar);
-            gb_tma_load_2d_pair(st + A_BYTES, &tma_b, kb * GB_BK, n0, bar);
+          if (elect_one()) {
+            uint8_t* st = smem + s * STAGE_BYTES;
+            if constexpr (PAIR == 1) {
+              mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
+              tma_load_2d(st, &tma_a, kb * GB_BK, m0, &full[s]);
+              tma_load_2d(st + A_BYTES, &tma_b, kb * GB_BK, n0, &full[s]);
+            } else {
+              // both CTAs' copies complete on the LEADER's barrier (it expects the bytes of the pair)
+              if (leader) mbar_arrive_expect_tx(&full[s], 2 * STAGE_BYTES);
+              const uint32_t bar = full0_cluster + (uint32_t)(s * 8);
+              gb_tma_load_2d_pair(st, &tma_a, kb * GB_BK, m0, bar);
+              gb_tma_load_2d_pair(st + A_BYTES, &tma_b, kb * GB_BK, n0, bar);
+            }
           }
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
-    } else if (warp == EW + 3 && lane == 0 && leader) {
-      // ================================ MMA issuer (pair leader only) ================================
+    } else if (warp == EW + 3 && leader) {
+      // ================================ MMA issuer (pair leader only; one elected lane issues) ====================
       constexpr uint32_t idesc = MODE == 0 ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, GB_BM * PAIR, GB_BN)
                                            : umma_idesc(2 /*s32*/, 1 /*s8*/, 1, GB_BM * PAIR, GB_BN);
       int s = 0, a = 0;
@@ -267,21 +278,25 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           const uint64_t adesc = desc0 + (uint64_t)((uint32_t)(s * STAGE_BYTES) >> 4);
           const uint64_t bdesc = adesc + (A_BYTES >> 4);
           const uint32_t d = tmem_base + a * GB_BN;
+          const bool last_kb = kb == p.kb_total - 1;
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < GB_BK / 32; ++k) {
-            const uint32_t accum = MODE == 0 ? (k > 0) : (kb > 0 || k > 0);
-            gb_umma<PAIR, MODE>(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+            for (int k = 0; k < GB_BK / 32; ++k) {
+              const uint32_t accum = MODE == 0 ? (k > 0) : (kb > 0 || k > 0);
+              gb_umma<PAIR, MODE>(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+            }
+            gb_commit<PAIR>(&empty[s]);
+            if (MODE == 0 || last_kb) gb_commit<PAIR>(&tfull[a]);
           }
-          gb_commit<PAIR>(&empty[s]);
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
-          if (MODE == 0 || kb == p.kb_total - 1) {
-            gb_commit<PAIR>(&tfull[a]);
+          if (MODE == 0 || last_kb) {
             if (++a == NBUF) { a = 0; aph ^= 1; }
           }
         }
       }
 #ifdef GB_PROF
-      if (p.prof) {
+      if (p.prof && lane == 0) {
         p.prof[blockIdx.x * 8 + 0] = clock64() - pm_t0;
         p.prof[blockIdx.x * 8 + 1] = pm_tempty;
         p.prof[blockIdx.x * 8 + 2] = pm_full;
@@ -333,7 +348,26 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           mbar_wait(&tfull[a], aph);
           tc_fence_after();
           uint32_t r[32];
-          if constexpr (EW == 16) {
+          if constexpr (GB_PROBE != 0) {
+            if (GB_PROBE & 8) release(a);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              if (GB_PROBE & 2) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) r[j] = (uint32_t)(kb + j);
+              } else {
+                tmem_ld_32x32(lane_addr + a * GB_BN + 32 * h, r);
+                gb_ld_wait32(r);
+              }
+              if (h == 1 && !(GB_PROBE & 8)) release(a);
+              if (GB_PROBE & 4) {
+                acc[h].x += __uint_as_float(r[0]) + __uint_as_float(r[31]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) gb_fma2(acc[16 * h + j], r[2 * j], r[2 * j + 1], sc);
+              }
+            }
+          } else if constexpr (EW == 16) {
             // 112 registers: one 32-column block in flight; the buffer is released after the second load
             tmem_ld_32x32(lane_addr + a * GB_BN, r);
             gb_ld_wait32(r);

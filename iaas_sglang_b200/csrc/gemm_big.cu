@@ -525,9 +525,13 @@ int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw,
   bp.sb = sb; bp.sb_sk = sb_sk; bp.sb_sn = sb_sn;
   bp.bias = bias; bp.out = out; bp.ldo = ldo; bp.out_bf16 = out_bf16;
   bp.M = M; bp.N = N; bp.K = K;
-  const int pair = tune(TUNE_GB_PAIR), bn = tune(TUNE_GB_BN);
+  const int pair = tune(TUNE_GB_PAIR);
+  int bn = tune(TUNE_GB_BN);   // 0 = by shape
   if (mode == 0) {
-    // knob gb_pair: bit 2 (value 4) selects cta_group::2 pairs for fp8 too; gb_bn: tile width 128 / 256
+    // 256-wide tiles are the faster pipeline (2112 vs 1880 TFLOP/s at 8192^3) but a skinny problem has too few of them
+    // to put every SM's copy engine to work: below ~3/4 of a wave of 256-wide tiles take 128-wide ones
+    if (bn == 0) bn = ((M + GB_BM - 1) / GB_BM) * ((N + 255) / 256) >= 112 ? 256 : 128;
+    // knob gb_pair = 4 selects cta_group::2 pairs for fp8 too (measured slower: the per-k-block release crosses the pair)
     if (pair == 4 && M > GB_BM) {
       if (bn == 128) return launch_big_t<0, 2, 128>(a, lda, w, ldw, bp, st);
       return launch_big_t<0, 2, 256>(a, lda, w, ldw, bp, st);

@@ -180,7 +180,9 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
   // after the k-loop the (drained) stage ring is reused: send[P][128] fp32 then recv[S-1][slice][128]
   float* send = reinterpret_cast<float*>(smem);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // (shuffle: provably warp-uniform for the compiler -> the service roles keep their state in uniform registers and
+  // issue UTMALDG / UTCxMMA / UTCBAR without an ELECT + R2UR.BROADCAST loop around each one; see gemm_big.cu)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int tile = blockIdx.x;
   SK_STAMP(0);
   const int S = p.splits;
@@ -215,62 +217,78 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
   griddep_launch();  // let the next kernel of the stream start its prologue (no-op without PDL)
 
-  if (warp < SK_NONEPI && warp != 1 && warp != 2 && lane == 0) {
+  if (warp == 0 || warp == 3) {
     // ================================ TMA producers (k-block i belongs to producer i % SK_NPROD) ================================
-    // One thread keeps only a few tensor copies in flight (measured: ~one box per 0.5 us per issuing thread whatever
-    // the box size, tools/tma_probe.cu), so six warps issue.
+    // whole warp in the loop (uniform control flow), one elected lane issues
     const int pidx = warp == 0 ? 0 : 1;
     const uint64_t pol_w = make_policy_evict_first();
     // weights do not depend on the previous kernel: fill the ring with them before waiting for it
     const int pre = nkb < p.stages ? nkb : p.stages;
     const uint32_t tx_bytes = MODE == 2 ? RAW_BYTES + ((p.debug & 8) ? 0 : x_bytes) : ((p.debug & 8) ? SK_BN * SK_BK : stage_bytes);
-    for (int i = pidx; i < pre; i += SK_NPROD) {
-      mbar_arrive_expect_tx(&full[i], tx_bytes);
-      if (MODE == 2) tma_load_2d_hint(smem + i * stage_bytes + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[i], pol_w);
-      else tma_load_2d_hint(smem + i * stage_bytes, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[i], pol_w);
+    const bool issuer = elect_one();
+    int i = pidx;
+    for (; i < pre; i += SK_NPROD) {
+      if (issuer) {
+        mbar_arrive_expect_tx(&full[i], tx_bytes);
+        if (MODE == 2) tma_load_2d_hint(smem + i * stage_bytes + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[i], pol_w);
+        else tma_load_2d_hint(smem + i * stage_bytes, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[i], pol_w);
+      }
     }
     griddep_wait();
-    for (int i = pidx; i < pre; i += SK_NPROD)
-      if (!(p.debug & 8)) tma_load_2d(smem + i * stage_bytes + SK_BN * SK_BK, &tma_x, SK_KB(i) * SK_BK, 0, &full[i]);
-    int i = pidx;
-    while (i < pre) i += SK_NPROD;
-    for (; i < nkb; i += SK_NPROD) {
-      const int s = i % p.stages;
-      const uint32_t ph = (i / p.stages) & 1;
-      mbar_wait(&empty[s], ph ^ 1);
-      mbar_arrive_expect_tx(&full[s], tx_bytes);
-      uint8_t* st = smem + s * stage_bytes;
-      if (MODE == 2) tma_load_2d_hint(st + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[s], pol_w);
-      else tma_load_2d_hint(st, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[s], pol_w);
-      if (!(p.debug & 8)) tma_load_2d(st + SK_BN * SK_BK, &tma_x, SK_KB(i) * SK_BK, 0, &full[s]);
+    if (!(p.debug & 8)) {
+      for (int j = pidx; j < pre; j += SK_NPROD)
+        if (issuer) tma_load_2d(smem + j * stage_bytes + SK_BN * SK_BK, &tma_x, SK_KB(j) * SK_BK, 0, &full[j]);
     }
-  } else if (warp == 1 && lane == 0) {
-    // ================================ MMA issuer ================================
+    // i >= stages from here on: stage / phase kept incrementally (no division by the run-time ring depth)
+    int sidx = i - p.stages;
+    uint32_t ph = 1;
+    while (sidx >= p.stages) { sidx -= p.stages; ph ^= 1; }
+    for (; i < nkb; i += SK_NPROD) {
+      mbar_wait(&empty[sidx], ph ^ 1);
+      if (issuer) {
+        mbar_arrive_expect_tx(&full[sidx], tx_bytes);
+        uint8_t* st = smem + sidx * stage_bytes;
+        if (MODE == 2) tma_load_2d_hint(st + SK_BN * SK_BK + x_bytes, &tma_w, tile * 64, SK_KB(i) * 64, &full[sidx], pol_w);
+        else tma_load_2d_hint(st, &tma_w, SK_KB(i) * SK_BK, tile * SK_BN, &full[sidx], pol_w);
+        if (!(p.debug & 8)) tma_load_2d(st + SK_BN * SK_BK, &tma_x, SK_KB(i) * SK_BK, 0, &full[sidx]);
+      }
+      __syncwarp();
+      sidx += SK_NPROD;
+      if (sidx >= p.stages) { sidx -= p.stages; ph ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer (one elected lane) ================================
     const uint32_t hfmt = p.out_bf16 ? 1u : 0u;  // kind::f16 operand format: 0 = f16, 1 = bf16
     const uint32_t idesc = MODE == 0   ? umma_idesc(1 /*f32*/, 0 /*e4m3*/, 0, SK_BN, p.mt_pad)
                            : MODE == 1 ? umma_idesc(2 /*s32*/, 1 /*s8*/, 1, SK_BN, p.mt_pad)
                                        : umma_idesc(1 /*f32*/, hfmt, hfmt, SK_BN, p.mt_pad);
+    int sidx = 0, a = 0;
+    uint32_t ph = 0, aph = 0;
+    const uint64_t desc0 = umma_desc_k_sw128(smem_u32(smem));
     for (int i = 0; i < nkb; ++i) {
-      const int s = i % p.stages;
-      const uint32_t ph = (i / p.stages) & 1;
-      const int a = MODE == 0 ? (i % NBUF) : 0;
-      if (MODE == 0) mbar_wait(&tempty[a], ((i / NBUF) & 1) ^ 1);
-      mbar_wait(&full[s], ph);
-      if (MODE == 2) mbar_wait(&afull[s], ph);
+      if (MODE == 0) mbar_wait(&tempty[a], aph ^ 1);
+      mbar_wait(&full[sidx], ph);
+      if (MODE == 2) mbar_wait(&afull[sidx], ph);
       tc_fence_after();
-      const uint32_t w_addr = smem_u32(smem + s * stage_bytes);
-      const uint64_t adesc = umma_desc_k_sw128(w_addr);
-      const uint64_t bdesc = umma_desc_k_sw128(w_addr + SK_BN * SK_BK);
+      const uint64_t adesc = desc0 + (uint64_t)((uint32_t)(sidx * stage_bytes) >> 4);
+      const uint64_t bdesc = adesc + ((SK_BN * SK_BK) >> 4);
       const uint32_t d = tmem_base + a * BUFCOLS;
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < SK_BK / 32; ++k) {
-        const uint32_t accum = MODE == 0 ? (k > 0) : (i > 0 || k > 0);
-        if (MODE == 0) umma_f8f6f4(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
-        else if (MODE == 1) umma_i8(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
-        else umma_f16(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+        for (int k = 0; k < SK_BK / 32; ++k) {
+          const uint32_t accum = MODE == 0 ? (k > 0) : (i > 0 || k > 0);
+          if (MODE == 0) umma_f8f6f4(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+          else if (MODE == 1) umma_i8(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+          else umma_f16(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
+        }
+        tc_commit(&empty[sidx]);
+        if (MODE == 0 || i == nkb - 1) tc_commit(&tfull[a]);
       }
-      tc_commit(&empty[s]);
-      if (MODE == 0 || i == nkb - 1) tc_commit(&tfull[a]);
+      __syncwarp();
+      if (++sidx == p.stages) { sidx = 0; ph ^= 1; }
+      if (MODE == 0) {
+        if (++a == NBUF) { a = 0; aph ^= 1; }
+      }
     }
   }
 
@@ -515,12 +533,17 @@ size_t skinny_workspace_bytes(int, int, int) { return 2048 * 8 * 8; }  // (devel
 
 bool skinny_applicable(int M) { return M <= 256; }
 
-// FP8 block-scaled crossover to the persistent large-M kernel (knob sk_max_m, default 128).  Measured
-// (tools/kb_cross.py): at M = 256 the large-M kernel is 1.4-3.4x faster on every cfg 2/4 TP shape (N 7168 K 4096:
-// 50.2 -> 22.1 us); at M <= 128 the skinny kernel wins.
-bool skinny_applicable_fp8(int M) {
+// FP8 block-scaled: skinny (swap-AB, cluster split-K) or the persistent large-M kernel?  Measured policy
+// (tools/kb_cross.py over the TP-local shapes of cfg 2/4/5, profiles/r02_kb_cross.txt): the large-M kernel wins at every
+// M > 128 and wherever the K loop is short (K <= 3584) or there are many n-tiles at K <= 4096; the skinny kernel wins on
+// long-K, few-tile shapes, where its split-K puts every SM to work.  Knob sk_max_m >= 0 forces "skinny iff M <= sk_max_m".
+bool skinny_applicable_fp8(int M, int N, int K) {
   const int max_m = tune(TUNE_SK_MAX_M);
-  return M <= (max_m > 256 ? 256 : max_m);
+  if (max_m >= 0) return M <= (max_m > 256 ? 256 : max_m);
+  if (M > 128) return false;
+  if (K <= 3584) return false;
+  if (K <= 4096 && N >= 6144) return false;
+  return true;
 }
 
 struct SkinnyPlan {

@@ -371,7 +371,7 @@ extern "C" int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const vo
   const int arch = b200_sm_arch();
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED,
                "fp8_blockwise_scaled_mm: requires an sm_100 device (got sm_%d); no fallback", arch);
-  if (skinny_applicable_fp8(M)) {
+  if (skinny_applicable_fp8(M, N, K)) {
     SkinnyParams sp{};
     sp.sa = sa; sp.sa_sm = sa_sm; sp.sa_sk = sa_sk;
     sp.sb = sb; sp.sb_sk = sb_sk; sp.sb_sn = sb_sn;

@@ -34,12 +34,12 @@ unsigned long long launch_count() { return __atomic_load_n(&g_launches, __ATOMIC
 struct TuneEntry { const char* name; const char* env; int def; };
 static const TuneEntry kTune[TUNE_COUNT] = {
     {"pdl", "B200_PDL", 1},               // programmatic dependent launch between the kernels of a step
-    {"sk_max_m", "B200_SK_MAX_M", 128},   // FP8: largest M served by the skinny (decode) kernel
+    {"sk_max_m", "B200_SK_MAX_M", -1},    // FP8: >= 0 forces "skinny kernel iff M <= value"; -1 = measured (M, N, K) policy
     {"sk_stages", "B200_SK_STAGES", 0},   // cap on the skinny kernel's TMA ring depth (0 = as many as fit)
     {"sk_splits", "B200_SK_SPLITS", 0},   // force the split-K cluster size (0 = heuristic)
     {"sk_debug", "B200_SK_DEBUG", 0},
     {"gb_pair", "B200_GB_PAIR", 2},       // large-M kernel: 2 = cta_group::2 pairs where M allows
-    {"gb_bn", "B200_GB_BN", 128},
+    {"gb_bn", "B200_GB_BN", 0},          // large-M fp8 tile width: 128 / 256, 0 = chosen by shape
     {"gb_prof", "B200_GB_PROF", 0},
     {"awq_nt", "B200_AWQ_NT", 0},
     {"awq_splits", "B200_AWQ_SPLITS", 0},

@@ -43,7 +43,7 @@ ref = None
 if os.environ.get("ZERO"):
     a.view(torch.uint8).zero_(); w.view(torch.uint8).zero_()
 for pair in (2, 4):
-    for bn in (128, 256):
+    for bn in (128, 256, 0):
         for dbg in (0,):
             _lib.tune_set("gb_pair", pair)
             _lib.tune_set("gb_bn", bn)

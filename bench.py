@@ -291,6 +291,7 @@ class DecodeStack(StackBase):
         wl = self.wl
         self.collectives = collectives
         self.no_fused = False
+        self.probe = None
         self.dtype = torch.bfloat16
         hq, hkv, d, hidden, inter = wl["hq"], wl["hkv"], wl["d"], wl["hidden"], wl["inter"]
         assert hq % tp == 0 and inter % tp == 0 and (hkv % tp == 0 or tp % hkv == 0)
@@ -361,32 +362,42 @@ class DecodeStack(StackBase):
         self.norm_f = torch.ones(hidden, dtype=self.dtype, device=dev)
         self._init_step_buffers(batch, hidden, ctx, table, dev)
 
-    def forward(self) -> torch.Tensor:
-        """One decode step over the static buffers (eager; also the body that gets graph-captured)."""
+    def attn_block(self, l, x, fused):
+        """qkv linear -> RoPE -> paged decode attention (fused KV append) -> o_proj: this rank's row-parallel partial"""
         from iaas_sglang_b200 import ops
 
-        fb, d = self.fb, self.d
+        d = self.d
+        qkv = self.method.apply_quantized(self.w_qkv[l], x[0], x[1], self.dtype) if fused else self.method.apply(self.w_qkv[l], x)
+        q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
+        ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
+        if fused:   # the attention merge kernel emits the group-128 quantisation of its output itself
+            a = self.attn[l](q, k, v, self.fb, quant_fp8=True)
+            return self.method.apply_quantized(self.w_o[l], a[0], a[1], self.dtype)
+        return self.method.apply(self.w_o[l], self.attn[l](q, k, v, self.fb))
+
+    def mlp_block(self, l, x, fused):
+        """gate_up linear -> SiLU*mul -> down linear: this rank's row-parallel partial"""
+        from iaas_sglang_b200 import ops
+
+        if fused:
+            gu = self.method.apply_quantized(self.w_gate_up[l], x[0], x[1], self.dtype)
+            act = ops.silu_and_mul_quant_fp8(gu)
+            return self.method.apply_quantized(self.w_down[l], act[0], act[1], self.dtype)
+        return self.method.apply(self.w_down[l], ops.silu_and_mul(self.method.apply(self.w_gate_up[l], x)))
+
+    def forward(self) -> torch.Tensor:
+        """One decode step over the static buffers (eager; also the body that gets graph-captured)."""
         h = self.hidden_in
         residual = torch.zeros_like(h)
         fused = hasattr(self.method, "apply_quantized") and not self.no_fused
         for l in range(self.L):
             # FP8: the norm / activation / all-reduce kernels emit the group-128 quantisation themselves (bit-identical)
             x = self._norm(h, self.norm1[l], residual, reduce=l > 0, quant=fused)   # residual += [allreduce](h) ; x = norm(residual)
-            qkv = self.method.apply_quantized(self.w_qkv[l], x[0], x[1], self.dtype) if fused else self.method.apply(self.w_qkv[l], x)
-            q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
-            ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
-            if fused:
-                a = self.attn[l](q, k, v, fb, quant_fp8=True)
-                h = self.method.apply_quantized(self.w_o[l], a[0], a[1], self.dtype)     # row-parallel partial
-            else:
-                h = self.method.apply(self.w_o[l], self.attn[l](q, k, v, fb))
+            h = self.attn_block(l, x, fused)
             x = self._norm(h, self.norm2[l], residual, reduce=True, quant=fused)
-            if fused:
-                gu = self.method.apply_quantized(self.w_gate_up[l], x[0], x[1], self.dtype)
-                act = ops.silu_and_mul_quant_fp8(gu)
-                h = self.method.apply_quantized(self.w_down[l], act[0], act[1], self.dtype)
-            else:
-                h = self.method.apply(self.w_down[l], ops.silu_and_mul(self.method.apply(self.w_gate_up[l], x)))
+            if l == 0 and self.probe is not None:
+                self.probe["residual_after_first_reduce"] = residual.clone()
+            h = self.mlp_block(l, x, fused)
         return self._norm(h, self.norm_f, residual, reduce=True, quant=False)
 
     # ---- algorithmic work (SURVEY 8d) ----
@@ -824,40 +835,89 @@ def time_allreduce(cx: Ctx, rows: int, hidden: int):
 
 
 def tp_check(cx: Ctx, wl: dict):
-    """N > 1: two layers of the headline model, sharded over the N ranks with the own all-reduce (the very code path
-    that is timed), against the UNSHARDED stack on the same weights (rank 0).  Also: every rank holds bit-identical
-    outputs, and no all-reduce gave up on a peer (b200_ar_error)."""
+    """N > 1 gate, run before anything is timed, on two layers of the headline model with every rank's shard cut from
+    ONE full set of weights:
+      1. emulation: rank 0 recomputes all N shards on its own GPU and combines their bf16 partials the way the all-reduce
+         kernels define it (fp32 sum in rank order, one rounding) -- the distributed output (the very code path that is
+         timed: own NVLink kernels, fused all-reduce + add + RMSNorm + FP8 quant) must equal it BIT FOR BIT;
+      2. every rank holds bit-identical outputs; no all-reduce gave up on a peer (b200_ar_error);
+      3. against the UNSHARDED stack: the hidden state after the first reduction (o_proj of layer 0) within 1e-2 -- TP
+         only re-orders that sum and rounds the partials to bf16.  The deviation of the final output is reported too; it
+         is larger because every later FP8 activation quantisation amplifies a last-bit difference (a code flip is a 6 %
+         step), with NCCL + separate kernels just as with ours -- (1) is what pins the kernels."""
     import torch.distributed as dist
 
-    from iaas_sglang_b200 import tp as tpmod
+    from iaas_sglang_b200 import ops, tp as tpmod
 
-    B, ctx = 8 * cx.world, 384
-    sh = DecodeStack(wl, 2, B, cx.world, cx.rank, cx.dev, collectives=True, shared_weights=True, ctx=ctx)
+    B, ctx, W = 8 * cx.world, 384, cx.world
+    sh = DecodeStack(wl, 2, B, W, cx.rank, cx.dev, collectives=True, shared_weights=True, ctx=ctx)
+    sh.probe = {}
     sh.upload()
     sh.backend.init_forward_metadata(sh.fb)
     out = sh.forward().clone()
+    mid = sh.probe["residual_after_first_reduce"]
     torch.cuda.synchronize()
-    gathered = [torch.empty_like(out) for _ in range(cx.world)]
+    gathered = [torch.empty_like(out) for _ in range(W)]
     dist.all_gather(gathered, out)
     identical = all(torch.equal(gathered[0], g) for g in gathered[1:])
-    rel = -1.0
     del sh
     torch.cuda.empty_cache()
+    res = torch.zeros(4, device=cx.dev, dtype=torch.float64)   # emulation equal, rel mid, rel final, spare
     if cx.rank == 0:
+        # ---- 1. all N shards on this GPU, partials combined in rank order ----
+        shards = [DecodeStack(wl, 2, B, W, r, cx.dev, collectives=False, shared_weights=True, ctx=ctx) for r in range(W)]
+        for st in shards:
+            st.upload()
+            st.backend.init_forward_metadata(st.fb)
+        residual = torch.zeros_like(shards[0].hidden_in)
+
+        def reduce_norm(parts, w, quant):
+            acc = parts[0].float()
+            for p_ in parts[1:]:
+                acc = acc + p_.float()
+            x = acc.to(parts[0].dtype)
+            return ops.rmsnorm_quant_fp8(x, w, 1e-5, residual=residual) if quant else ops.rmsnorm(x, w, 1e-5, residual=residual)
+
+        s0 = shards[0]
+        x = ops.rmsnorm_quant_fp8(s0.hidden_in, s0.norm1[0], 1e-5, residual=residual)
+        for l in range(2):
+            if l > 0:
+                x = reduce_norm(parts, s0.norm1[l], True)   # noqa: F821
+            parts = [st.attn_block(l, x, True) for st in shards]
+            x = reduce_norm(parts, s0.norm2[l], True)
+            if l == 0:
+                emu_mid = residual.clone()
+            parts = [st.mlp_block(l, x, True) for st in shards]
+        emu = reduce_norm(parts, s0.norm_f, False)
+        res[0] = 1.0 if torch.equal(emu, out) else 0.0
+        res[3] = ((emu_mid.float() - mid.float()).norm() / emu_mid.float().norm()).item()
+        del shards, parts, x, emu
+        torch.cuda.empty_cache()
+        # ---- 3. the unsharded stack ----
         ref = DecodeStack(wl, 2, B, 1, 0, cx.dev, collectives=False, shared_weights=True, ctx=ctx)
+        ref.probe = {}
         ref.upload()
         ref.backend.init_forward_metadata(ref.fb)
         r = ref.forward().float()
-        rel = ((out.float() - r).norm() / r.norm()).item()
+        rm = ref.probe["residual_after_first_reduce"].float()
+        res[1] = ((mid.float() - rm).norm() / rm.norm()).item()
+        res[2] = ((out.float() - r).norm() / r.norm()).item()
         del ref
-    t = torch.tensor([rel], device=cx.dev, dtype=torch.float64)
-    dist.broadcast(t, 0)
+    dist.broadcast(res, 0)
     car = tpmod.custom_all_reduce()
     err = car.error() if car is not None else 0
     torch.cuda.empty_cache()
-    return {"rel_l2_vs_unsharded": round(t.item(), 6), "tolerance": 1e-2, "bit_identical_across_ranks": bool(identical),
-            "ar_error": int(err), "layers": 2, "batch": B, "ctx": ctx,
-            "allreduce": "own kernels" if car is not None else "ncclAllReduce"}
+    # (NVSwitch multicast reductions add the W copies in the switch's own order: one rounding of the half type around the
+    # rank-order sum, tools/ar_check.py -- then the emulation is held to 4e-3 after the first reduction instead of bits)
+    nvls = car is not None and car.multicast and W > 2
+    emu_ok = res[0].item() == 1.0 or (nvls and 0 <= res[3].item() < 4e-3)
+    ok = bool(emu_ok and identical and err == 0 and 0 <= res[1].item() < 1e-2)
+    return {"ok": ok, "bit_identical_to_rank_order_emulation": bool(res[0].item() == 1.0),
+            "rel_l2_vs_emulation_after_first_reduce": round(res[3].item(), 8), "bit_identical_across_ranks": bool(identical), "ar_error": int(err),
+            "rel_l2_vs_unsharded_after_first_reduce": round(res[1].item(), 6), "tolerance": 1e-2,
+            "rel_l2_vs_unsharded_final_output": round(res[2].item(), 6), "layers": 2, "batch": B, "ctx": ctx,
+            "allreduce": f"own kernels ({car.setup}, multicast {'yes' if car.multicast else 'no'}), fused with add + RMSNorm + FP8 quant"
+            if car is not None else "ncclAllReduce"}
 
 
 def gemm_roofline(dev):
@@ -1066,10 +1126,10 @@ def main():
     if world > 1 and not args.no_tp_check and wl["quant"] == "fp8" and wl.get("arch") != "mla":
         check = tp_check(cx, wl)
         log(f"[bench] tp_check {check}")
-        if not (0 <= check["rel_l2_vs_unsharded"] < check["tolerance"]) or not check["bit_identical_across_ranks"] or check["ar_error"]:
+        if not check["ok"]:
             if rank == 0:
                 emit({"metric": "decode tok/s", "value": None, "n_gpus": world, "tp_check": check,
-                      "error": "tensor-parallel output differs from the unsharded output: nothing was timed"})
+                      "error": "tensor-parallel output failed the parity gate: nothing was timed"})
             sys.stdout.flush()
             os._exit(3)
 

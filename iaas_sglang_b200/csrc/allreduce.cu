@@ -455,16 +455,20 @@ extern "C" void b200_ar_destroy(void* ctx) {
 //   mapping), 4 = rows kernel, one-shot pull; 0 = leave it to ncclAllReduce.
 // `multicast` = the context has a multicast mapping.  The reference makes the same kind of split
 // (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one stage, else two).
+// Measured policy (tools/ar_check.py AR_SWEEP=1 on 2 / 4 / 8 B200 of one NVSwitch box, profiles/r02_allreduce.md; us):
+//   2 ranks: one-shot everywhere (1 MB 14.7, 4 MB 22.0; NCCL 21.6 / 45);
+//   4 ranks: one-shot up to 3 MB (1 MB 19.9, 2 MB 25.8), two-shot above (4 MB 31.8, 8 MB 42.8; NVLS 47.9 / 58.2,
+//            NCCL 44.2 / 53.2) -- the multicast kernel never wins at 4 ranks;
+//   8 ranks: one-shot up to 768 KB (64 KB 18.7, 512 KB 24.7), then NVLS where the buffer has a multicast mapping
+//            (1 MB 27.9, 2 MB 29.6, 4 MB 35.0; two-shot 29.7 / 31.7 / 35.9; NCCL 36.2 / 39.8 / 61.0), two-shot from 6 MB
+//            (8 MB 47.0 vs NVLS 58.6, NCCL 77.9).  No size is left to NCCL any more.
+// 1 one-shot, 2 two-shot, 3 NVLS rows kernel; 0 = leave it to NCCL.
 extern "C" int b200_ar_mode2(int world, size_t bytes, int multicast) {
   if (world < 2 || world > AR_MAX_RANKS) return 0;
   if (world == 2) return 1;
-  if (multicast) {
-    if (world <= 4) return bytes <= ((size_t)1 << 20) ? 1 : 3;
-    return bytes <= ((size_t)256 << 10) ? 1 : 3;
-  }
-  if (world <= 4) return bytes <= ((size_t)6 << 20) ? 1 : 2;
-  if (bytes <= (size_t)1536 * 1024) return 1;
-  if (bytes < ((size_t)3 << 20)) return 0;
+  if (world <= 4) return bytes <= ((size_t)3 << 20) ? 1 : 2;
+  if (bytes <= (size_t)768 * 1024) return 1;
+  if (multicast && bytes < ((size_t)6 << 20)) return 3;
   return 2;
 }
 extern "C" int b200_ar_mode(int world, size_t bytes) { return b200_ar_mode2(world, bytes, 0); }
@@ -605,9 +609,17 @@ extern "C" int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* re
   const size_t bytes = (size_t)M * H * 2;
   int mode = c->mode > 0 ? c->mode : b200_ar_mode2(p.world, bytes, p.mc != nullptr);
   bool nvls = (mode == 3) && p.mc;
-  if (!nvls && c->mode <= 0 && p.world > 4 && bytes > ((size_t)1536 << 10)) {
-    set_error("ar_allreduce_add_rmsnorm: %zu bytes at %d ranks without a multicast mapping: run the two kernels", bytes, p.world);
-    return B200_ERR_UNSUPPORTED;
+  if (c->mode <= 0) {
+    // One kernel or two?  Measured (tools/ar_check.py, fused vs all-reduce -> rmsnorm_quant_fp8, us): 2 ranks 128x4096
+    // 18.3 vs 19.2, 256x8192 37.6 vs 30; 4 ranks 256x4096 33.6 vs 33.0, 128x5120 35.8 vs 32.3, 256x8192 53.2 vs 59.7;
+    // 8 ranks 512x4096 47.2 vs 42.5, 128x5120 47.5 vs 34.7, 256x8192 46.7 vs 60.7.  The fused kernel wins on wide rows
+    // (H = 8192: the separate norm is a 16 KB row per CTA) and on small messages at 2 ranks; elsewhere the caller runs the
+    // two kernels (B200_ERR_UNSUPPORTED is that answer, tp.py falls back; every rank decides from (world, M, H) alone).
+    const bool fused_wins = p.world == 2 ? bytes <= ((size_t)1536 << 10) : H >= 8192;
+    if (!fused_wins || (!nvls && p.world > 4 && bytes > ((size_t)1536 << 10))) {
+      set_error("ar_allreduce_add_rmsnorm: %d x %d at %d ranks: the two separate kernels are the faster plan", M, H, p.world);
+      return B200_ERR_UNSUPPORTED;
+    }
   }
   RowNormArgs e;
   e.residual = (uint16_t*)residual; e.w = (const uint16_t*)weight; e.out = (uint16_t*)norm_out; e.q = (uint8_t*)q; e.q_sm = q_sm;

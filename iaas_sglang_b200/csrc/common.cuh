@@ -161,6 +161,16 @@ __device__ __forceinline__ void bulk_g2s_hint(void* dst_smem, const void* src_gm
 __device__ __forceinline__ void cp_async_16(uint32_t dst_smem, const void* src_gmem) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
 }
+// the same with an L2 prefetch hint: touching one 16-byte chunk pulls the whole aligned 256 / 128 bytes into L2
+__device__ __forceinline__ void cp_async_16_l2_256(uint32_t dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.cg.shared.global.L2::256B [%0], [%1], 16;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_16_l2_128(uint32_t dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.cg.shared.global.L2::128B [%0], [%1], 16;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_16_hint(uint32_t dst_smem, const void* src_gmem, uint64_t policy) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src_gmem), "l"(policy) : "memory");
+}
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }

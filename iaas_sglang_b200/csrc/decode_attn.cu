@@ -323,24 +323,50 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
           }
         };
         load_idx(0, lo, hi);
+        // The issue rate of these warps is what bounds the short-row path (a longer instruction sequence per row showed
+        // up one-to-one in the kernel time), so the loop is kept to a shuffle, two 32 x 32 -> 64-bit multiply-adds and
+        // the two copies per pair of rows: int32 page-table entries (the usual req_to_token dtype) with byte strides
+        // that fit 32 bits; the new token's substitution is only looked for in the tile that can hold it.
+        const bool fast32 = !p.idx64 && p.kb_st * 2 < (int64_t)1 << 31 && p.vb_st * 2 < (int64_t)1 << 31;
+        const uint32_t kst_b = (uint32_t)(p.kb_st * 2), vst_b = (uint32_t)(p.vb_st * 2);
+        const char* kbase = reinterpret_cast<const char*>(p.k_buf + kvh0 * p.kb_sh) + chunk * 16;
+        const char* vbase = reinterpret_cast<const char*>(p.v_buf + kvh0 * p.vb_sh) + chunk * 16;
+        const bool unit_tail = p.fused_new && cur.tile + n == cur.tiles_b;   // the segment ends at the request's last token
         for (int it = 0; it < n; ++it, ++gt) {
           const int s = gt % C::STAGES;
           const uint32_t ph = (gt / C::STAGES) & 1;
           if (it + 1 < n) load_idx(it + 1, nlo, nhi);
           mbar_wait(&empty[s], ph ^ 1);
-          const int64_t idx = p.idx64 ? (((int64_t)hi << 32) | (uint32_t)lo) : (int64_t)lo;
           const uint32_t kdst = smem_u32(smem + s * C::STAGE_BYTES) + (pw * RW + sub) * C::ROW_PITCH + chunk * 16;
+          if (fast32 && !(unit_tail && it == n - 1)) {
 #pragma unroll
-          for (int r = 0; r < RW; r += RPI) {
-            const int64_t ri = __shfl_sync(0xffffffffu, idx, r + sub);
-            const uint16_t* ks = p.k_buf + ri * p.kb_st + kvh0 * p.kb_sh;
-            const uint16_t* vs = p.v_buf + ri * p.vb_st + kvh0 * p.vb_sh;
-            if (ri == loc_b) {
-              ks = knew_row;
-              vs = vnew_row;
+            for (int r = 0; r < RW; r += RPI) {
+              const uint32_t ri = (uint32_t)__shfl_sync(0xffffffffu, lo, r + sub);
+              const char* ks = kbase + (uint64_t)ri * kst_b;
+              const char* vs = vbase + (uint64_t)ri * vst_b;
+              if constexpr (C::ROW_BYTES >= 256) {
+                // L2::256B: the first chunk of a row pulls its whole aligned 256 bytes into L2 (one DRAM request per row)
+                cp_async_16_l2_256(kdst + r * C::ROW_PITCH, ks);
+                cp_async_16_l2_256(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs);
+              } else {
+                cp_async_16(kdst + r * C::ROW_PITCH, ks);
+                cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs);
+              }
             }
-            cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 8);
-            cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 8);
+          } else {
+            const int64_t idx = p.idx64 ? (((int64_t)hi << 32) | (uint32_t)lo) : (int64_t)lo;
+#pragma unroll 4
+            for (int r = 0; r < RW; r += RPI) {
+              const int64_t ri = __shfl_sync(0xffffffffu, idx, r + sub);
+              const uint16_t* ks = p.k_buf + ri * p.kb_st + kvh0 * p.kb_sh;
+              const uint16_t* vs = p.v_buf + ri * p.vb_st + kvh0 * p.vb_sh;
+              if (ri == loc_b) {
+                ks = knew_row;
+                vs = vnew_row;
+              }
+              cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 8);
+              cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 8);
+            }
           }
           cp_async_mbar_arrive_noinc(&full[s]);
           lo = nlo;

@@ -45,7 +45,7 @@ static const TuneEntry kTune[TUNE_COUNT] = {
     {"awq_splits", "B200_AWQ_SPLITS", 0},
     {"awq_debug", "B200_AWQ_DEBUG", 0},
     {"awq_v1", "B200_AWQ_V1", 0},
-    {"attn_bulk_min", "B200_ATTN_BULK_MIN", 0},
+    {"attn_ld_hint", "B200_ATTN_LD_HINT", 0},   // short-row KV loads: 0 = L2::256B prefetch hint, 1 = plain cp.async.cg
     {"gb_epi", "B200_GB_EPI", 0},
 };
 static int g_tune[TUNE_COUNT];

@@ -218,6 +218,12 @@ def bench_prof():
     attn_case("cfg3tp4", 128, 10, 2, 128, 4096)
 
 
+def bench_proftp8():
+    """a few plain launches of the TP8-local attention shapes (Hkv 1: 256-byte rows) for ncu (-k regex:decode_attn_mma)"""
+    _plain_timeit()
+    attn_case("cfg2tp8", 512, 4, 1, 128, 4096)
+
+
 def bench_profgemm():
     """a few plain launches of decode-shape GEMMs for ncu (-k regex:gemm_skinny)"""
     global timeit

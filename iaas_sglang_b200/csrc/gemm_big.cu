@@ -215,6 +215,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   if constexpr (PAIR == 2) gb_cluster_sync(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();  // programmatic dependent launch: the next kernel of the stream may start its prologue
 
   if (warp >= EW) {
     gb_setmaxnreg_dec<SVC_REGS>();
@@ -223,11 +224,36 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       const uint32_t full0_cluster = PAIR == 2 ? gb_mapa(smem_u32(&full[0]), 0) : 0;
       int s = 0;
       uint32_t ph = 0;
+      // weights do not depend on the previous kernel of the stream: the first ring-full of W tiles is requested before
+      // griddepcontrol.wait, the activations after it (decode-shape calls: the ramp of this GEMM overlaps its predecessor)
+      int pre = 0;
+      if constexpr (PAIR == 1) {
+        if (worker < p.n_tiles) {
+          int tm, tn;
+          gb_tile_coord(p, worker, tm, tn);
+          pre = p.kb_total < stages ? p.kb_total : stages;
+          if (elect_one()) {
+            for (int kb = 0; kb < pre; ++kb) {
+              mbar_arrive_expect_tx(&full[kb], STAGE_BYTES);
+              tma_load_2d(smem + kb * STAGE_BYTES + A_BYTES, &tma_b, kb * GB_BK, tn * GB_BN, &full[kb]);
+            }
+          }
+          __syncwarp();
+        }
+      }
+      griddep_wait();
       for (int t = worker; t < p.n_tiles; t += p.workers) {
         int tm, tn;
         gb_tile_coord(p, t, tm, tn);
         const int m0 = (tm * PAIR + rank) * GB_BM, n0 = tn * GB_BN + rank * B_ROWS;
         for (int kb = 0; kb < p.kb_total; ++kb) {
+          if (pre > 0) {   // this stage's W tile is already in flight (first tile only): add the activations
+            --pre;
+            if (elect_one()) tma_load_2d(smem + s * STAGE_BYTES, &tma_a, kb * GB_BK, m0, &full[s]);
+            __syncwarp();
+            if (++s == stages) { s = 0; ph ^= 1; }
+            continue;
+          }
           mbar_wait(&empty[s], ph ^ 1);
           if (elect_one()) {
             uint8_t* st = smem + s * STAGE_BYTES;
@@ -307,6 +333,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   } else {
     // ================================ epilogue warps ================================
     gb_setmaxnreg_inc<EPI_REGS>();
+    griddep_wait();   // the activation scales (and the output buffer) belong to the stream order
     const int quad = warp & 3, cg = warp >> 2;  // TMEM lanes [32*quad, +32), columns [64*cg, +64)
     const int row_in_tile = quad * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + cg * 64;
@@ -484,13 +511,15 @@ static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, 
   cfg.blockDim = dim3(GB_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = PAIR;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = PAIR;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = PAIR > 1 ? 1 : 0;
+  cfg.numAttrs = PAIR > 1 ? 2 : 1;
 #ifdef GB_PROF
   const int prof = tune(TUNE_GB_PROF);
   static long long* dprof = nullptr;

@@ -62,6 +62,7 @@ class ExtendAttnParams(C.Structure):
         ("B", C.c_int32), ("Hq", C.c_int32), ("Hkv", C.c_int32), ("D", C.c_int32), ("Dv", C.c_int32),
         ("max_len_extend", C.c_int32), ("dtype", C.c_int32),
         ("sm_scale", c_float), ("logit_cap", c_float),
+        ("prefix_only", C.c_int32), ("reserved0", C.c_int32), ("lse_out", c_void_p),
     ]
 
 
@@ -143,7 +144,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.b200_abi_version() != 2:
+    if lib.b200_abi_version() != 3:
         raise ImportError("libb200sgl.so ABI version mismatch")
     _lib = lib
     return lib

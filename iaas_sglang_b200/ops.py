@@ -453,8 +453,11 @@ def cutlass_mla_decode(q_nope: torch.Tensor, q_pe: torch.Tensor, kv_c_and_k_pe_c
 
 
 def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices, seq_lens,
-                     extend_seq_lens, extend_start_loc, max_len_extend: int, sm_scale: float, logit_cap: float):
-    """Same positional signature as torch.ops.sgl_kernel.extend_attention_cpu (torch_extension_cpu.cpp:271-275)."""
+                     extend_seq_lens, extend_start_loc, max_len_extend: int, sm_scale: float, logit_cap: float, *,
+                     prefix_only: bool = False, lse_out: Optional[torch.Tensor] = None):
+    """Same positional signature as torch.ops.sgl_kernel.extend_attention_cpu (torch_extension_cpu.cpp:271-275).
+    Keyword-only extras (no reference counterpart): prefix_only -- every new token attends to exactly the prefix
+    (the shared-prefix half of cascade decode); lse_out -- float32 [T, Hq] natural-log LSE per row for merge_state."""
     dev = require_cuda(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices,
                        seq_lens, extend_seq_lens, extend_start_loc)
     for t in (q_extend, k_extend, v_extend, k_buffer, v_buffer):
@@ -480,6 +483,11 @@ def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer,
     p.max_len_extend = int(max_len_extend)
     p.dtype = DTYPE_CODE[q_extend.dtype]
     p.sm_scale, p.logit_cap = float(sm_scale), float(logit_cap)
+    p.prefix_only = int(bool(prefix_only))
+    if lse_out is not None:
+        if lse_out.dtype != torch.float32 or tuple(lse_out.shape) != (T, Hq) or not lse_out.is_contiguous():
+            raise RuntimeError("lse_out must be a contiguous float32 [T, Hq] tensor")
+        p.lse_out = lse_out.data_ptr()
     with torch.cuda.device(dev):
         check(load().b200_extend_attn(p, current_stream(dev)))
     return o_extend

@@ -40,7 +40,7 @@ extern "C" {
 #define B200_F16 1
 #define B200_F32 2
 
-#define B200_SGL_ABI_VERSION 2
+#define B200_SGL_ABI_VERSION 3
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -166,6 +166,13 @@ typedef struct b200_extend_attn_params {
   int32_t dtype;
   float sm_scale;
   float logit_cap;
+  /* ABI v3.  prefix_only != 0: every new token attends to exactly the request's prefix (no new keys, no causal mask):
+   * the shared-prefix half of cascade decode (sgl-kernel/csrc/attention/cascade.cu merges the two halves).
+   * lse_out: optional float [T_ext, Hq], natural-log log-sum-exp of every row's scaled logits (-inf for an empty key
+   * set), the `s` operand of merge_state.  Both need the tuned kernel (D == Dv in {64, 128}). */
+  int32_t prefix_only;
+  int32_t reserved0;
+  void* lse_out;
 } b200_extend_attn_params;
 int b200_extend_attn(const b200_extend_attn_params* p, void* stream);
 

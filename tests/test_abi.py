@@ -30,13 +30,13 @@ def test_library_exports_every_declared_symbol():
     raw = ctypes.CDLL(_lib.SO_PATH)
     for s in declared_symbols():
         assert hasattr(raw, s), s
-    assert lib.b200_abi_version() == 2
+    assert lib.b200_abi_version() == 3
 
 
 def test_struct_layout_matches_header():
     # v1: 23 pointer/int64/size_t fields (8 B) + 10 int32 + 2 float = 232 bytes; v2 adds 2 int32 + 5 pointer/int64
     assert ctypes.sizeof(_lib.DecodeAttnParams) == 23 * 8 + 12 * 4 + 2 * 4 + 5 * 8
-    assert ctypes.sizeof(_lib.ExtendAttnParams) == 22 * 8 + 10 * 4
+    assert ctypes.sizeof(_lib.ExtendAttnParams) == 22 * 8 + 10 * 4 + 2 * 4 + 8   # v3: prefix_only, reserved, lse_out
 
 
 def test_size_queries_need_no_gpu():

@@ -314,7 +314,9 @@ class DecodeStack(StackBase):
                 self.kv_pool.v_buffer[l].normal_(generator=gen)
 
         runner = compat.ModelRunnerStub(compat.ModelConfigStub(hq, hkv, d, ctx), self.r2t_pool, self.kv_pool, device=dev, tp_size=tp)
-        self.backend = B200AttnBackend(runner)
+        # workloads with a RadixAttention shared prefix run the cascade path: the shared KV rows are read once per batch
+        self.cascade = bool(shared) and os.environ.get("B200_BENCH_CASCADE", "1") != "0"
+        self.backend = B200AttnBackend(runner, cascade=self.cascade)
         self.attn = [compat.RadixAttention(self.hq, d, d ** -0.5, self.hkv, l) for l in range(layers)]
 
         # ---- weights ----
@@ -1077,7 +1079,10 @@ def run_extra(cx: Ctx, name: str, args, lib, peak, peak_src):
     stack = make_stack(wl, layers, batch, tp, cx.rank, cx.dev, collectives=cx.world > 1)
     torch.cuda.synchronize()
     m = measure_stack(cx, stack, max(3, min(args.steps, 10)), 3, e2e=False, lib=lib)
-    rec = {"name": name, "config": workload_config(wl, name, layers, batch, tp), "dtype": dtype_string(wl),
+    cfg = workload_config(wl, name, layers, batch, tp)
+    if getattr(stack, "cascade", False):
+        cfg["attention"] = "cascade decode: shared prefix attended once per batch (extend kernel, prefix_only) + per-request suffix, LSE merge"
+    rec = {"name": name, "config": cfg, "dtype": dtype_string(wl),
            "value": round(batch / (m["ms"] / layers * wl["layers"] * 1e-3), 1),
            "unit": f"tok/s ({layers}-layer slice timed, extrapolated linearly over the model's {wl['layers']} identical layers)",
            "slice_ms_per_step": round(m["ms"], 4), "ms_per_layer": round(m["ms"] / layers, 4),

@@ -42,6 +42,7 @@ class DecodeAttnParams(C.Structure):
         ("meta_i32_mask", C.c_int32), ("page_size", C.c_int32),
         ("q_rope", c_void_p), ("qrope_stride_b", c_int64), ("qrope_stride_h", c_int64),
         ("k_rope_new", c_void_p), ("krope_stride_b", c_int64),
+        ("kv_start", c_void_p), ("cascade_o", c_void_p), ("cascade_lse", c_void_p), ("prefix_o", c_void_p), ("prefix_lse", c_void_p),
     ]
 
 
@@ -62,7 +63,7 @@ class ExtendAttnParams(C.Structure):
         ("B", C.c_int32), ("Hq", C.c_int32), ("Hkv", C.c_int32), ("D", C.c_int32), ("Dv", C.c_int32),
         ("max_len_extend", C.c_int32), ("dtype", C.c_int32),
         ("sm_scale", c_float), ("logit_cap", c_float),
-        ("prefix_only", C.c_int32), ("reserved0", C.c_int32), ("lse_out", c_void_p),
+        ("prefix_only", C.c_int32), ("reserved0", C.c_int32), ("lse_out", c_void_p), ("out_f32", c_void_p),
     ]
 
 
@@ -83,6 +84,9 @@ SIGNATURES = {
     "b200_set_kv_buffer": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64,
                                    c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_extend_attn": (c_int, [C.POINTER(ExtendAttnParams), c_void_p]),
+    "b200_merge_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    "b200_shared_prefix_len": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                       c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200_create_kv_indices": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                        c_void_p]),
     "b200_create_page_table": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,

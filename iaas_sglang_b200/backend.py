@@ -16,6 +16,7 @@ Differences that matter for speed, not for results:
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -42,7 +43,7 @@ class ForwardMetadata:
 
 
 class B200AttnBackend(_Base):
-    def __init__(self, model_runner, skip_prefill: bool = False, kv_indptr_buf=None):
+    def __init__(self, model_runner, skip_prefill: bool = False, kv_indptr_buf=None, cascade: Optional[bool] = None):
         super().__init__()
         self.forward_metadata: Optional[ForwardMetadata] = None
         self.device = model_runner.device
@@ -59,6 +60,16 @@ class B200AttnBackend(_Base):
         self.static_kv_splits = 0  # 0 = heuristic (cf. SGLANG_TRITON_DECODE_ATTN_STATIC_KV_SPLITS, triton_backend.py:111-113)
         self.cuda_graph_attn_logits: Optional[torch.Tensor] = None
         self.cuda_graph_max_bs = 0
+        # Cascade (shared-prefix) decode, SURVEY 8f rank 4: when every request of a decode batch starts with the same KV
+        # slots (RadixAttention prefix sharing), the shared rows are attended to ONCE for the whole batch and merged by
+        # LSE with each request's own suffix (sgl-kernel/csrc/attention/cascade.cu; FlashInfer's cascade wrapper).  Off
+        # by default (it costs one small kernel per layer when nothing is shared): server_args.b200_cascade / B200_CASCADE=1
+        # / cascade=True.  GQA/MHA with head_dim in {64, 128} only; anything else stays on the plain path.
+        if cascade is None:
+            cascade = bool(getattr(getattr(model_runner, "server_args", None), "b200_cascade", False)) or os.environ.get("B200_CASCADE", "0") == "1"
+        self.cascade = bool(cascade) and self.head_dim == self.v_head_dim and self.head_dim in (64, 128)
+        self.cascade_state: Optional[ops.CascadeState] = None
+        self._dtype = model_runner.token_to_kv_pool.get_key_buffer(0).dtype
 
     # ------------------------------------------------------------------ metadata
     def _splits_and_scratch(self, bs: int, max_seq_len: int, scratch: Optional[torch.Tensor] = None):
@@ -80,6 +91,8 @@ class B200AttnBackend(_Base):
             prev = self.forward_metadata.attn_logits if self.forward_metadata is not None else None
             S, scratch = self._splits_and_scratch(bs, max_seq_len, prev)
             self.forward_metadata = ForwardMetadata(scratch, S, max_seq_len, None)
+            if self.cascade and forward_batch.forward_mode.is_decode() and bs > 0:
+                self._cascade_detect(bs, forward_batch.req_pool_indices, forward_batch.seq_lens)
         else:
             cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
             if cpu is not None:
@@ -87,6 +100,13 @@ class B200AttnBackend(_Base):
             else:
                 max_extend_len = int(torch.max(forward_batch.extend_seq_lens).item())
             self.forward_metadata = ForwardMetadata(None, 1, 0, max_extend_len)
+
+    def _cascade_detect(self, bs: int, req_pool_indices, seq_lens):
+        """once per step: the shared page-table prefix of the batch, left on the device (ops.CascadeState)"""
+        st = self.cascade_state
+        if st is None or st.max_bs < bs:
+            st = self.cascade_state = ops.CascadeState(max(bs, self.cuda_graph_max_bs), self.num_head, self.v_head_dim, self._dtype, self.device)
+        st.detect(self.req_to_token, req_pool_indices, seq_lens)
 
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int = 0, kv_indices_buf=None):
         """Fixed scratch for every captured batch size (cuda_graph_runner.py:140-187)."""
@@ -97,6 +117,8 @@ class B200AttnBackend(_Base):
                                                 self.max_context_len, self.static_kv_splits)
             need = max(need, ops.decode_attention_workspace_bytes(bs, self.num_head, self.v_head_dim, S))
         self.cuda_graph_attn_logits = torch.empty((need + 3) // 4, dtype=torch.float32, device=self.device)
+        if self.cascade:   # static buffers: the captured kernels read the prefix length from them at replay time
+            self.cascade_state = ops.CascadeState(max_bs, self.num_head, self.v_head_dim, self._dtype, self.device)
 
     def init_forward_metadata_capture_cuda_graph(self, bs: int, num_tokens: int, req_pool_indices, seq_lens, encoder_lens,
                                                  forward_mode, spec_info):
@@ -108,6 +130,8 @@ class B200AttnBackend(_Base):
         # the split count is baked into the captured launch: size it for the longest context
         S, _ = self._splits_and_scratch(bs, self.max_context_len, self.cuda_graph_attn_logits)
         self.forward_metadata = ForwardMetadata(self.cuda_graph_attn_logits, S, self.max_context_len, None)
+        if self.cascade and forward_mode.is_decode():
+            self._cascade_detect(bs, req_pool_indices, seq_lens)
 
     def init_forward_metadata_replay_cuda_graph(self, bs: int, req_pool_indices, seq_lens, seq_lens_sum: int, encoder_lens,
                                                 forward_mode, spec_info, seq_lens_cpu=None):
@@ -117,6 +141,8 @@ class B200AttnBackend(_Base):
             raise NotImplementedError("b200 attention backend: speculative decoding is not supported")
         if not forward_mode.is_decode_or_idle():
             raise ValueError("Invalid forward mode")
+        if self.cascade and forward_mode.is_decode():   # eager, before graph.replay(): one scan of the page table
+            self._cascade_detect(bs, req_pool_indices[:bs], seq_lens[:bs])
 
     def get_cuda_graph_seq_len_fill_value(self):
         return 1  # triton_backend.py:629-630
@@ -153,12 +179,16 @@ class B200AttnBackend(_Base):
             else:
                 key = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
                 value = v.view(-1, layer.tp_v_head_num, layer.v_head_dim) if v is not None else None
+        casc = None
+        if self.cascade and self.cascade_state is not None and q_rope is None and qv.shape[0] <= self.cascade_state.max_bs:
+            casc = self.cascade_state
+            casc.prefix_attention(qv, k_buf, v_buf, forward_batch.req_to_token_pool.req_to_token, layer.scaling, layer.logit_cap)
         res = ops.decode_attention(
             qv, k_buf, v_buf, o.view(-1, H, layer.v_head_dim), key, value, forward_batch.out_cache_loc,
             md.attn_logits, forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             forward_batch.seq_lens, layer.scaling, layer.logit_cap,
             max_seq_len=md.max_seq_len, num_splits=md.num_kv_splits, fused_kv_write=True, quant_fp8=bool(quant_fp8),
-            q_rope=q_rope, k_rope=kr)
+            q_rope=q_rope, k_rope=kr, cascade=casc)
         if quant_fp8:
             return res[1], res[2]
         return o

@@ -15,7 +15,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 SO = os.path.join(HERE, "libb200sgl.so")
-SOURCES = ["runtime.cu", "elementwise.cu", "decode_attn.cu", "extend_attn.cu", "gemm_tc.cu", "gemm_skinny.cu", "gemm_big.cu", "awq_gemm.cu", "awq_fused.cu", "fused_elem.cu", "allreduce.cu"]
+SOURCES = ["runtime.cu", "elementwise.cu", "decode_attn.cu", "extend_attn.cu", "gemm_tc.cu", "gemm_skinny.cu", "gemm_big.cu", "awq_gemm.cu", "awq_fused.cu", "fused_elem.cu", "allreduce.cu", "cascade.cu"]
 HEADERS = ["common.cuh", "gemm_skinny.h", "decode_mla.cuh", "rmsnorm_row.cuh", os.path.join(ROOT, "include", "b200_sgl.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",

@@ -75,6 +75,14 @@ struct DecodeKParams {
   int is_mla;
   float sm_scale, logit_cap;
   MergeQuant mq;
+  // cascade / shared-prefix decode (tuned GQA path): the kernel attends to positions [*kv_start, seq_len) only, every
+  // (request, head) state goes through the merge kernel, which adds the state over the shared prefix [0, *kv_start)
+  // computed once for the whole batch (extend kernel, prefix_only)
+  const int32_t* kv_start;   // device scalar or nullptr
+  float* casc_o;             // [B, Hq, Dv] fp32: normalised suffix output of the units one CTA saw whole
+  float* casc_lse;           // [B, Hq] fp32, log2 domain
+  const float* pre_o;        // [B, Hq, Dv] fp32 prefix state
+  const float* pre_lse;      // [B, Hq] natural-log LSE of the prefix state (-inf: empty)
 };
 
 // seq_lens / req_pool_indices / out_cache_loc arrive as int64 (schedule_batch.py) or int32 (cuda_graph_runner.py:273-276)
@@ -183,8 +191,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
   // ---- batch tables + barriers ----
   griddep_wait();    // programmatic dependent launch: q / k_new / the batch tensors belong to the stream order
   griddep_launch();  // the merge kernel may be scheduled as soon as SM resources free up
+  const int64_t kv_start = p.kv_start ? (int64_t)*p.kv_start : 0;
   for (int b = threadIdx.x; b < p.B; b += kAttnThreads) {
-    int64_t len = seq_len_at(p, b);
+    int64_t len = seq_len_at(p, b) - kv_start;
     if (len < 0) len = 0;
     s_len[b] = (int32_t)len;
     s_rpi[b] = (int32_t)req_at(p, b);
@@ -252,7 +261,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
           vd[i] = vs[i];
         }
       }
-      const uint8_t* r2t_row = reinterpret_cast<const uint8_t*>(p.r2t) + (req * p.r2t_stride) * (p.idx64 ? 8 : 4);
+      const uint8_t* r2t_row = reinterpret_cast<const uint8_t*>(p.r2t) + (req * p.r2t_stride + kv_start) * (p.idx64 ? 8 : 4);
       if constexpr (C::BULK) {
         constexpr int ITEMS = 2 * RW;  // one K and one V bulk copy per row
         constexpr int R = (ITEMS + 31) / 32;
@@ -558,7 +567,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       const float inv = L > 0.f ? 1.f / L : 0.f;
       if (whole_unit) {
         const int head = (kvh0 + h) * p.G + row0 + r;
-        p.out[((int64_t)b * p.Hq + head) * Dv + dv] = float_to_half<BF16>(O * inv);
+        if (p.casc_o) {   // cascade: the merge kernel still has to add the shared-prefix state -> fp32 state, not the output
+          p.casc_o[((int64_t)b * p.Hq + head) * Dv + dv] = O * inv;
+          if (dv == 0) p.casc_lse[(int64_t)b * p.Hq + head] = L > 0.f ? M + log2f(L) : -INFINITY;
+        } else {
+          p.out[((int64_t)b * p.Hq + head) * Dv + dv] = float_to_half<BF16>(O * inv);
+        }
       } else {
         const int prow = slot_row0 + h * 16 + r;
         p.part_o[(int64_t)prow * Dv + dv] = O * inv;
@@ -605,16 +619,23 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
                                                                 uint16_t* out,
                                                                 const void* __restrict__ seq_lens, int lens32, int B, int Hq,
                                                                 int Ggrp, int HPC, int tile_t, int NG, int n_qblk,
-                                                                int grid, int Dv, const MergeQuant mq) {
+                                                                int grid, int Dv, const MergeQuant mq,
+                                                                const int32_t* __restrict__ kv_start_p,
+                                                                const float* __restrict__ casc_o,
+                                                                const float* __restrict__ casc_lse,
+                                                                const float* __restrict__ pre_o,
+                                                                const float* __restrict__ pre_lse) {
   griddep_wait();
   griddep_launch();
   const int lane = threadIdx.x & 31;
   const int hblocks = (Hq + 7) >> 3;
   const int b = blockIdx.x / hblocks, h = (blockIdx.x - b * hblocks) * 8 + (threadIdx.x >> 5);
   if (h >= Hq) return;
+  const int64_t kv_start = kv_start_p ? (int64_t)*kv_start_p : 0;
+  const bool cascade = casc_o != nullptr;
   int all = 0, before = 0, tiles_b = 0;
   for (int i = lane; i < B; i += 32) {
-    int64_t len = meta_at(seq_lens, i, lens32);
+    int64_t len = meta_at(seq_lens, i, lens32) - kv_start;
     if (len < 0) len = 0;
     const int tl = (int)((len + tile_t - 1) / tile_t);
     all += tl;
@@ -628,7 +649,7 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
     tiles_b += __shfl_xor_sync(0xffffffffu, tiles_b, o);
   }
   uint16_t* orow = out + ((int64_t)b * Hq + h) * Dv;
-  if (tiles_b == 0) {  // seq_len == 0: defined output (zeros)
+  if (tiles_b == 0 && !cascade) {  // seq_len == 0: defined output (zeros)
     for (int d = lane; d < Dv; d += 32) orow[d] = 0;
     if constexpr (QUANT) merge_quant_row<BF16>(mq, make_uint2(0u, 0u), b, h, lane);
     return;
@@ -638,14 +659,15 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   const int g = hg * n_qblk + qblk;
   const int64_t W = (int64_t)NG * all;
   const int64_t t0 = (int64_t)NG * before + (int64_t)g * tiles_b, t1 = t0 + tiles_b;
-  const int c0 = (int)part_owner(t0, W, grid), c1 = (int)part_owner(t1 - 1, W, grid);
-  if (c0 == c1) {  // one CTA saw the whole unit and wrote the output itself
+  const int c0 = tiles_b > 0 ? (int)part_owner(t0, W, grid) : 0, c1 = tiles_b > 0 ? (int)part_owner(t1 - 1, W, grid) : 0;
+  const bool whole = c0 == c1;  // one CTA saw the whole unit
+  if (whole && !cascade) {      // ... and wrote the output itself
     if constexpr (QUANT) merge_quant_row<BF16>(mq, *reinterpret_cast<const uint2*>(orow + lane * 4), b, h, lane);
     return;
   }
   // partial (o, lse) pairs of the CTAs c0..c1 (CTAs whose range is empty wrote nothing)
   const int rows = HPC * 16;
-  const int n = c1 - c0 + 1;  // <= grid <= kMaxPartials
+  const int n = (whole || tiles_b == 0) ? 0 : c1 - c0 + 1;  // <= grid <= kMaxPartials
   constexpr int R = kMaxPartials / 32;
   int prow[R];
   float w[R];
@@ -666,6 +688,14 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
     M = fmaxf(M, w[k]);
   }
   M = warp_max(M);
+  // cascade: two more states of this (request, head) -- the suffix state of a whole unit (fp32, written by the attention
+  // kernel instead of the output) and the state over the shared prefix (computed once for the batch; natural-log LSE)
+  float lse_w = -INFINITY, lse_p = -INFINITY;
+  if (cascade) {
+    if (whole && tiles_b > 0) lse_w = casc_lse[(int64_t)b * Hq + h];
+    lse_p = pre_lse[(int64_t)b * Hq + h] * kLog2e;
+    M = fmaxf(M, fmaxf(lse_w, lse_p));
+  }
   const float Mu = (M == -INFINITY) ? 0.f : M;
   float L = 0.f;
 #pragma unroll
@@ -674,10 +704,28 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
     L += w[k];
   }
   L = warp_sum(L);
+  const float w_w = lse_w > -INFINITY ? exp2f(lse_w - Mu) : 0.f, w_p = lse_p > -INFINITY ? exp2f(lse_p - Mu) : 0.f;
+  L += w_w + w_p;
   const float inv = L > 0.f ? 1.f / L : 0.f;
   float4 acc[NV];
 #pragma unroll
   for (int v = 0; v < NV; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (cascade) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const int d4 = lane + 32 * v;
+      if (d4 * 4 < Dv) {
+        if (w_w > 0.f) {
+          const float4 x = reinterpret_cast<const float4*>(casc_o + ((int64_t)b * Hq + h) * Dv)[d4];
+          acc[v].x += w_w * x.x; acc[v].y += w_w * x.y; acc[v].z += w_w * x.z; acc[v].w += w_w * x.w;
+        }
+        if (w_p > 0.f) {
+          const float4 x = reinterpret_cast<const float4*>(pre_o + ((int64_t)b * Hq + h) * Dv)[d4];
+          acc[v].x += w_p * x.x; acc[v].y += w_p * x.y; acc[v].z += w_p * x.z; acc[v].w += w_p * x.w;
+        }
+      }
+    }
+  }
 #pragma unroll
   for (int k = 0; k < R; ++k) {
     if (32 * k < n) {  // warp-uniform
@@ -728,13 +776,13 @@ static int launch_merge_part(const DecodeKParams& kp, int Ggrp, int HPC, int til
   const dim3 g(kp.B * ((kp.Hq + 7) / 8)), blk(256);
   if (kp.mq.q)  // Dv == 128 and an 8-byte aligned `out` were checked by the entry point
     launch_pdl(decode_merge_part_kernel<BF16, 1, true>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.meta32 & 1, kp.B, kp.Hq, Ggrp,
-               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
+               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq, kp.kv_start, (const float*)kp.casc_o, (const float*)kp.casc_lse, kp.pre_o, kp.pre_lse);
   else if (kp.Dv <= 128)
     launch_pdl(decode_merge_part_kernel<BF16, 1, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.meta32 & 1, kp.B, kp.Hq, Ggrp,
-               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
+               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq, kp.kv_start, (const float*)kp.casc_o, (const float*)kp.casc_lse, kp.pre_o, kp.pre_lse);
   else
     launch_pdl(decode_merge_part_kernel<BF16, 4, false>, g, blk, 0, st, kp.part_o, kp.part_lse, kp.out, kp.seq_lens, kp.meta32 & 1, kp.B, kp.Hq, Ggrp,
-               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq);
+               HPC, tile_t, NG, n_qblk, grid, kp.Dv, kp.mq, kp.kv_start, (const float*)kp.casc_o, (const float*)kp.casc_lse, kp.pre_o, kp.pre_lse);
   return launched("decode_merge_part_kernel launch");
 }
 
@@ -1029,6 +1077,12 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
   kp.B = a->B; kp.Hq = a->Hq; kp.Hkv = a->Hkv; kp.G = a->Hq / a->Hkv; kp.D = a->D; kp.Dv = a->Dv;
   kp.is_mla = is_mla; kp.sm_scale = a->sm_scale; kp.logit_cap = a->logit_cap;
   kp.mq = MergeQuant{};
+  kp.kv_start = (const int32_t*)a->kv_start;
+  kp.casc_o = (float*)a->cascade_o; kp.casc_lse = (float*)a->cascade_lse;
+  kp.pre_o = (const float*)a->prefix_o; kp.pre_lse = (const float*)a->prefix_lse;
+  const bool cascade = a->kv_start || a->cascade_o || a->cascade_lse || a->prefix_o || a->prefix_lse;
+  B200_REQUIRE(!cascade || (a->kv_start && a->cascade_o && a->cascade_lse && a->prefix_o && a->prefix_lse), B200_ERR_ARG,
+               "decode_attn: cascade needs kv_start, cascade_o, cascade_lse, prefix_o and prefix_lse together");
 
   // tuned path needs 16-byte aligned, head-contiguous rows
   bool mma = mma_path_ok(a->Hq, a->Hkv, a->D, a->Dv) && page_shift == 0;
@@ -1048,6 +1102,8 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
                  "decode_attn_quant_fp8: needs the tuned GQA kernel with Dv == 128 and aligned outputs (quantise separately otherwise)");
     kp.mq = *mq;
   }
+  B200_REQUIRE(!cascade || (mma && a->Dv % 4 == 0 && ((uintptr_t)a->prefix_o & 15) == 0 && ((uintptr_t)a->cascade_o & 15) == 0),
+               B200_ERR_UNSUPPORTED, "decode_attn: cascade needs the tuned GQA kernel (D == Dv in {64, 128}, aligned rows)");
   // tuned MLA path (decode_mla.cuh): 16-byte aligned latent rows, 4-byte aligned q rows; an explicit split-count
   // hint selects the generic kernel (the tuned kernel partitions the KV work itself)
   bool mla = mla_path_ok(a->Hkv, a->D, a->Dv, is_mla) && a->num_splits <= 1;

@@ -39,6 +39,7 @@ struct ExtendKParams {
   float sm_scale, logit_cap;
   int prefix_only;   // tuned kernel: every row attends to exactly the prefix (no new tokens, no causal mask)
   float* lse_out;    // tuned kernel: optional [T_ext, Hq] natural-log LSE
+  float* out_f32;    // tuned kernel: optional [T_ext, Hq, Dv] fp32 output instead of `out`; P is then kept exact (hi + lo)
 };
 
 template <int MAXE, bool BF16>
@@ -270,14 +271,21 @@ __global__ void __launch_bounds__(128) extend_attn_mma_kernel(const __grid_const
       m_run[r] = m_new;
     }
     // P is rounded to the KV dtype before P V, as the reference kernels do (extend_attention.py: p.to(v.dtype))
-    uint32_t pa[EX_BN / 16][4];
+    // (exact mode -- the fp32 state for cascade decode, which is held to the decode tolerance: P = hi + lo halves and
+    // a second PV pass, as the decode kernel does)
+    const bool exact = p.out_f32 != nullptr;
+    uint32_t pa[EX_BN / 16][4], pb[EX_BN / 16][4];
     float ps[2] = {0.f, 0.f};
 #pragma unroll
     for (int nt = 0; nt < EX_BN / 8; ++nt) {
       const float p0 = exp2f(sc[nt][0] - m_use[0]), p1 = exp2f(sc[nt][1] - m_use[0]);
       const float p2 = exp2f(sc[nt][2] - m_use[1]), p3 = exp2f(sc[nt][3] - m_use[1]);
-      pa[nt >> 1][(nt & 1) * 2 + 0] = pack_half2<BF16>(p0, p1);
-      pa[nt >> 1][(nt & 1) * 2 + 1] = pack_half2<BF16>(p2, p3);
+      const uint32_t h01 = pack_half2<BF16>(p0, p1), h23 = pack_half2<BF16>(p2, p3);
+      pa[nt >> 1][(nt & 1) * 2 + 0] = h01;
+      pa[nt >> 1][(nt & 1) * 2 + 1] = h23;
+      const float2 f01 = unpack_half2<BF16>(h01), f23 = unpack_half2<BF16>(h23);
+      pb[nt >> 1][(nt & 1) * 2 + 0] = pack_half2<BF16>(p0 - f01.x, p1 - f01.y);
+      pb[nt >> 1][(nt & 1) * 2 + 1] = pack_half2<BF16>(p2 - f23.x, p3 - f23.y);
       ps[0] += p0 + p1;
       ps[1] += p2 + p3;
     }
@@ -301,6 +309,10 @@ __global__ void __launch_bounds__(128) extend_attn_mma_kernel(const __grid_const
         ldsm_x4_t(vbase + kk * 16 * PITCH + v_lane_off + jp * 32, r0, r1, r2, r3);
         mma_16816<BF16>(o[2 * jp], pa[kk], r0, r1);
         mma_16816<BF16>(o[2 * jp + 1], pa[kk], r2, r3);
+        if (exact) {
+          mma_16816<BF16>(o[2 * jp], pb[kk], r0, r1);
+          mma_16816<BF16>(o[2 * jp + 1], pb[kk], r2, r3);
+        }
       }
     }
     __syncthreads();   // everyone is done with this stage before the tile after next lands in it
@@ -316,10 +328,16 @@ __global__ void __launch_bounds__(128) extend_attn_mma_kernel(const __grid_const
   for (int x = 0; x < 2; ++x) {
     if (!rvalid[x]) continue;
     const float inv = l_run[x] > 0.f ? 1.f / l_run[x] : 0.f;
-    uint16_t* orow = p.out + ((start + tok[x]) * p.Hq + head[x]) * (int64_t)D + 2 * t;
+    if (p.out_f32) {
+      float* frow = p.out_f32 + ((start + tok[x]) * p.Hq + head[x]) * (int64_t)D + 2 * t;
 #pragma unroll
-    for (int j = 0; j < D / 8; ++j)
-      *reinterpret_cast<uint32_t*>(orow + j * 8) = pack_half2<BF16>(o[j][2 * x] * inv, o[j][2 * x + 1] * inv);
+      for (int j = 0; j < D / 8; ++j) *reinterpret_cast<float2*>(frow + j * 8) = make_float2(o[j][2 * x] * inv, o[j][2 * x + 1] * inv);
+    } else {
+      uint16_t* orow = p.out + ((start + tok[x]) * p.Hq + head[x]) * (int64_t)D + 2 * t;
+#pragma unroll
+      for (int j = 0; j < D / 8; ++j)
+        *reinterpret_cast<uint32_t*>(orow + j * 8) = pack_half2<BF16>(o[j][2 * x] * inv, o[j][2 * x + 1] * inv);
+    }
     if (p.lse_out && t == 0)   // natural-log LSE of the row (-inf for an empty key set), for merge_state
       p.lse_out[(start + tok[x]) * p.Hq + head[x]] = l_run[x] > 0.f ? (m_run[x] + log2f(l_run[x])) / kLog2e : -INFINITY;
   }
@@ -360,7 +378,7 @@ extern "C" int b200_extend_attn(const b200_extend_attn_params* a, void* stream) 
                "extend_attn: bad sizes");
   B200_REQUIRE(a->D <= 1024 && a->Dv <= 1024, B200_ERR_UNSUPPORTED, "extend_attn: head dim > 1024");
   B200_REQUIRE(a->dtype == B200_BF16 || a->dtype == B200_F16, B200_ERR_UNSUPPORTED, "extend_attn: dtype must be bf16/f16");
-  B200_REQUIRE(a->q && a->k_ext && a->v_ext && a->out && a->k_buf && a->v_buf && a->req_to_token && a->req_pool_indices &&
+  B200_REQUIRE(a->q && a->k_ext && a->v_ext && (a->out || a->out_f32) && a->k_buf && a->v_buf && a->req_to_token && a->req_pool_indices &&
                    a->seq_lens && a->extend_seq_lens && a->extend_start_loc,
                B200_ERR_ARG, "extend_attn: null tensor");
   if (a->B == 0 || a->max_len_extend <= 0) return B200_OK;
@@ -376,7 +394,7 @@ extern "C" int b200_extend_attn(const b200_extend_attn_params* a, void* stream) 
   kp.r2t = a->req_to_token; kp.r2t_stride = a->req_to_token_stride; kp.idx64 = a->idx_is_i64;
   kp.rpi = a->req_pool_indices; kp.seq_lens = a->seq_lens; kp.ext_lens = a->extend_seq_lens; kp.ext_start = a->extend_start_loc;
   kp.Hq = a->Hq; kp.G = a->Hq / a->Hkv; kp.D = a->D; kp.Dv = a->Dv; kp.sm_scale = a->sm_scale; kp.logit_cap = a->logit_cap;
-  kp.prefix_only = a->prefix_only; kp.lse_out = (float*)a->lse_out;
+  kp.prefix_only = a->prefix_only; kp.lse_out = (float*)a->lse_out; kp.out_f32 = (float*)a->out_f32;
   const bool bf = a->dtype == B200_BF16;
   auto al16 = [](const void* ptr, int64_t s0, int64_t s1) { return ((uintptr_t)ptr & 15) == 0 && s0 % 8 == 0 && s1 % 8 == 0; };
   const bool tuned = a->D == a->Dv && (a->D == 64 || a->D == 128) && al16(a->k_ext, a->kext_stride_t, a->kext_stride_h) &&
@@ -390,8 +408,8 @@ extern "C" int b200_extend_attn(const b200_extend_attn_params* a, void* stream) 
     return bf ? launch_extend_mma<64, true>(kp, a->B, a->Hkv, a->max_len_extend, st)
               : launch_extend_mma<64, false>(kp, a->B, a->Hkv, a->max_len_extend, st);
   }
-  B200_REQUIRE(!a->prefix_only && !a->lse_out, B200_ERR_UNSUPPORTED,
-               "extend_attn: prefix_only / lse_out need the tuned kernel (D == Dv in {64, 128}, 16-byte aligned rows)");
+  B200_REQUIRE(!a->prefix_only && !a->lse_out && !a->out_f32, B200_ERR_UNSUPPORTED,
+               "extend_attn: prefix_only / lse_out / out_f32 need the tuned kernel (D == Dv in {64, 128}, 16-byte aligned rows)");
   dim3 grid(a->max_len_extend, a->Hq, a->B);
   return a->dtype == B200_BF16 ? launch_extend<true>(kp, grid, (cudaStream_t)stream)
                                : launch_extend<false>(kp, grid, (cudaStream_t)stream);

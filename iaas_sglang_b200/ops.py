@@ -299,7 +299,8 @@ _INT_META = (torch.int64, torch.int32)
 def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logits, req_to_token, req_pool_indices,
                      seq_lens, sm_scale: float, logit_cap: float, *, max_seq_len: int = 0, num_splits: int = 0,
                      fused_kv_write: bool = False, quant_fp8: bool = False, quant_eps: float = 1e-10,
-                     q_rope: Optional[torch.Tensor] = None, k_rope: Optional[torch.Tensor] = None, page_size: int = 1):
+                     q_rope: Optional[torch.Tensor] = None, k_rope: Optional[torch.Tensor] = None, page_size: int = 1,
+                     cascade: Optional["CascadeState"] = None):
     """Same positional signature as torch.ops.sgl_kernel.decode_attention_cpu (decode.cpp:1375-1388;
     schema torch_extension_cpu.cpp:264-268) on CUDA tensors.
 
@@ -313,6 +314,8 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     allocates them (cuda_graph_runner.py:273-276); req_pool_indices=None means request b owns row b of the table.
     MLA extras (cutlass_mla_backend.py:226-285): q_rope [B,Hq,64] with query = q_nope [B,Hq,512]; k_rope [B,1,64] with
     key = the latent part [B,1,512] (set_mla_kv_buffer); page_size P > 1: req_to_token is a [B, pages] page table.
+    cascade: a CascadeState (shared_prefix_len + the prefix state of this layer): the kernel attends to the positions
+    after the shared prefix only and its merge adds the prefix state -- same result, the shared KV rows are read once.
     quant_fp8=True also returns (x_q, x_s) = per_token_group_quant_fp8(output.view(B, Hq*Dv), 128,
     column_major_scales=True) for the FP8 block o_proj (fp8_utils.py:202-204), bit-identical to the separate call; the
     split-merge kernel emits it where the tuned kernel runs (Dv == 128), otherwise the quantiser is launched here.
@@ -382,6 +385,8 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     p.write_kv = write_kv
     p.max_seq_len = int(max_seq_len)
     p.sm_scale, p.logit_cap = float(sm_scale), float(logit_cap)
+    if cascade is not None:
+        cascade.bind(p, B, Hq, Dv, query.dtype)
     S = lib.b200_decode_attn_num_splits(B, Hq, Hkv, D, Dv, int(max_seq_len), int(num_splits)) if B > 0 else 1
     p.num_splits = S
     need = lib.b200_decode_attn_workspace_size(B, Hq, Dv, S)
@@ -403,6 +408,80 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
         else:
             check(rc)
     return output, x_q, x_s
+
+
+class CascadeState:
+    """Device-side state of cascade (shared-prefix) decode for one batch: the shared prefix length P and the one-request
+    view of the batch (b200_shared_prefix_len, once per step), scratch for the suffix states, and -- per layer -- the
+    prefix state (prefix_o, prefix_lse) written by extend_attention(prefix_only=True).  Everything lives in static
+    buffers and P stays on the device, so a captured CUDA graph follows the batch."""
+
+    def __init__(self, max_bs: int, Hq: int, Dv: int, dtype: torch.dtype, device, align: int = 128, min_len: int = 256):
+        self.max_bs, self.Hq, self.Dv, self.dtype, self.align, self.min_len = max_bs, Hq, Dv, dtype, align, min_len
+        self.scratch = torch.full((1,), 0x7FFFFFFF, dtype=torch.int32, device=device)
+        self.prefix_len = torch.zeros(1, dtype=torch.int32, device=device)
+        self.one_seq_len = torch.zeros(1, dtype=torch.int64, device=device)
+        self.one_req = torch.zeros(1, dtype=torch.int64, device=device)
+        self.one_start = torch.zeros(1, dtype=torch.int64, device=device)
+        self.ext_lens = {}     # batch size -> int64 [1] device tensor (extend_seq_lens of the one-request view)
+        self.casc_o = torch.empty(max_bs, Hq, Dv, dtype=torch.float32, device=device)
+        self.casc_lse = torch.empty(max_bs, Hq, dtype=torch.float32, device=device)
+        self.prefix_o = torch.empty(max_bs, Hq, Dv, dtype=torch.float32, device=device)
+        self.prefix_lse = torch.empty(max_bs, Hq, dtype=torch.float32, device=device)
+
+    def detect(self, req_to_token, req_pool_indices, seq_lens) -> None:
+        """Once per decode step (before the layers): P = shared page-table prefix of the batch, on the device."""
+        B = seq_lens.numel()
+        dev = seq_lens.device
+        meta = int(seq_lens.dtype == torch.int32) | (int(req_pool_indices is not None and req_pool_indices.dtype == torch.int32) << 1)
+        with torch.cuda.device(dev):
+            check(load().b200_shared_prefix_len(ptr(req_to_token), int(req_to_token.dtype == torch.int64), req_to_token.stride(0),
+                                                ptr(req_pool_indices), ptr(seq_lens), meta, B, self.align, self.min_len,
+                                                ptr(self.scratch), ptr(self.prefix_len), ptr(self.one_seq_len), ptr(self.one_req),
+                                                current_stream(dev)))
+
+    def prefix_attention(self, query, k_cache, v_cache, req_to_token, sm_scale: float, logit_cap: float) -> None:
+        """Per layer: the state of every (request, head) over the shared prefix, computed ONCE for the batch -- the B
+        queries are the `new tokens` of one request whose prefix is the shared one (tuned extend kernel, prefix_only)."""
+        B = query.shape[0]
+        if B not in self.ext_lens:
+            self.ext_lens[B] = torch.full((1,), B, dtype=torch.int64, device=query.device)
+        extend_attention(query, query[:, :k_cache.shape[1]], query[:, :k_cache.shape[1]], None, k_cache, v_cache,
+                         req_to_token, self.one_req, self.one_seq_len, self.ext_lens[B], self.one_start, B, sm_scale, logit_cap,
+                         prefix_only=True, lse_out=self.prefix_lse[:B], out_f32=self.prefix_o[:B])
+
+    def bind(self, p, B: int, Hq: int, Dv: int, dtype) -> None:
+        if B > self.max_bs or Hq != self.Hq or Dv != self.Dv or dtype != self.dtype:
+            raise RuntimeError("CascadeState was sized for another batch / head shape")
+        p.kv_start = self.prefix_len.data_ptr()
+        p.cascade_o, p.cascade_lse = self.casc_o.data_ptr(), self.casc_lse.data_ptr()
+        p.prefix_o, p.prefix_lse = self.prefix_o.data_ptr(), self.prefix_lse.data_ptr()
+
+
+def merge_state(v_a: torch.Tensor, s_a: torch.Tensor, v_b: torch.Tensor, s_b: torch.Tensor,
+                v_merged: Optional[torch.Tensor] = None, s_merged: Optional[torch.Tensor] = None):
+    """sgl_kernel.merge_state (sgl-kernel/python/sgl_kernel/attention.py:12-28; csrc/attention/cascade.cu:12-55): the
+    attention states (V [T, H, D], S = natural-log LSE [T, H]) of the same queries over two disjoint key sets -> the
+    state over their union.  Returns (v_merged, s_merged)."""
+    dev = require_cuda(v_a, s_a, v_b, s_b, v_merged, s_merged)
+    if v_a.dim() != 3 or s_a.dim() != 2 or v_a.shape != v_b.shape or s_a.shape != s_b.shape or v_a.shape[:2] != s_a.shape:
+        raise RuntimeError("merge_state: v_a / v_b must be [T, H, D] and s_a / s_b [T, H]")   # cascade.cu:22-31
+    if v_a.dtype not in DTYPE_CODE or v_a.dtype == torch.float32 or v_b.dtype != v_a.dtype:
+        raise RuntimeError("merge_state: v_a / v_b must share a bf16/f16 dtype")
+    s_a, s_b = s_a.to(torch.float32).contiguous(), s_b.to(torch.float32).contiguous()
+    v_a, v_b = v_a.contiguous(), v_b.contiguous()
+    if v_merged is None:
+        v_merged = torch.empty_like(v_a)
+    if s_merged is None:
+        s_merged = torch.empty_like(s_a)
+    T, H, D = v_a.shape
+    with torch.cuda.device(dev):
+        check(load().b200_merge_state(ptr(v_a), ptr(s_a), ptr(v_b), ptr(s_b), ptr(v_merged), ptr(s_merged), T, H, D,
+                                      DTYPE_CODE[v_a.dtype], current_stream(dev)))
+    return v_merged, s_merged
+
+
+merge_state_v2 = merge_state   # attention.py:31-52: same contract, another kernel in the reference
 
 
 def cutlass_mla_get_workspace_size(max_seq_len: int, num_batches: int, sm_count: int = 0, num_kv_splits: int = 1) -> int:
@@ -454,10 +533,11 @@ def cutlass_mla_decode(q_nope: torch.Tensor, q_pe: torch.Tensor, kv_c_and_k_pe_c
 
 def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices, seq_lens,
                      extend_seq_lens, extend_start_loc, max_len_extend: int, sm_scale: float, logit_cap: float, *,
-                     prefix_only: bool = False, lse_out: Optional[torch.Tensor] = None):
+                     prefix_only: bool = False, lse_out: Optional[torch.Tensor] = None, out_f32: Optional[torch.Tensor] = None):
     """Same positional signature as torch.ops.sgl_kernel.extend_attention_cpu (torch_extension_cpu.cpp:271-275).
     Keyword-only extras (no reference counterpart): prefix_only -- every new token attends to exactly the prefix
-    (the shared-prefix half of cascade decode); lse_out -- float32 [T, Hq] natural-log LSE per row for merge_state."""
+    (the shared-prefix half of cascade decode); lse_out -- float32 [T, Hq] natural-log LSE per row for merge_state;
+    out_f32 -- float32 [T, Hq, Dv] output instead of o_extend (which may be None), softmax weights kept exact."""
     dev = require_cuda(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer, req_to_token, req_pool_indices,
                        seq_lens, extend_seq_lens, extend_start_loc)
     for t in (q_extend, k_extend, v_extend, k_buffer, v_buffer):
@@ -465,14 +545,20 @@ def extend_attention(q_extend, k_extend, v_extend, o_extend, k_buffer, v_buffer,
             raise RuntimeError("q/k/v tensors must be 3-d and contiguous in the last dimension")
     T, Hq, D = q_extend.shape
     Hkv, Dv = k_buffer.shape[1], v_buffer.shape[2]
-    if tuple(o_extend.shape) != (T, Hq, Dv) or not o_extend.is_contiguous():
+    if o_extend is None and out_f32 is None:
+        raise RuntimeError("o_extend (or out_f32) is required")
+    if o_extend is not None and (tuple(o_extend.shape) != (T, Hq, Dv) or not o_extend.is_contiguous()):
         raise RuntimeError("o_extend must be a contiguous [T, Hq, Dv] tensor")
+    if out_f32 is not None and (out_f32.dtype != torch.float32 or tuple(out_f32.shape) != (T, Hq, Dv) or not out_f32.is_contiguous()):
+        raise RuntimeError("out_f32 must be a contiguous float32 [T, Hq, Dv] tensor")
     rpi, sl, el, es = _i64(req_pool_indices), _i64(seq_lens), _i64(extend_seq_lens), _i64(extend_start_loc)
     p = _lib.ExtendAttnParams()
     p.q, p.q_stride_t, p.q_stride_h = q_extend.data_ptr(), q_extend.stride(0), q_extend.stride(1)
     p.k_ext, p.kext_stride_t, p.kext_stride_h = k_extend.data_ptr(), k_extend.stride(0), k_extend.stride(1)
     p.v_ext, p.vext_stride_t, p.vext_stride_h = v_extend.data_ptr(), v_extend.stride(0), v_extend.stride(1)
-    p.out = o_extend.data_ptr()
+    p.out = o_extend.data_ptr() if o_extend is not None else None
+    if out_f32 is not None:
+        p.out_f32 = out_f32.data_ptr()
     p.k_buf, p.kbuf_stride_t, p.kbuf_stride_h = k_buffer.data_ptr(), k_buffer.stride(0), k_buffer.stride(1)
     p.v_buf, p.vbuf_stride_t, p.vbuf_stride_h = v_buffer.data_ptr(), v_buffer.stride(0), v_buffer.stride(1)
     p.req_to_token, p.req_to_token_stride = req_to_token.data_ptr(), req_to_token.stride(0)

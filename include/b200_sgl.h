@@ -114,6 +114,18 @@ typedef struct b200_decode_attn_params {
   int64_t qrope_stride_b, qrope_stride_h;
   const void* k_rope_new;
   int64_t krope_stride_b;
+  /* ABI v3 -- cascade / shared-prefix decode (sgl-kernel/csrc/attention/cascade.cu, merge_attn_states.cu; FlashInfer's
+   * cascade wrapper does the same split).  All five or none; tuned GQA kernel only.
+   *   kv_start     device int32 scalar P (b200_shared_prefix_len): the kernel attends to positions [P, seq_len) only;
+   *   cascade_o    float [B, Hq, Dv], cascade_lse float [B, Hq]: scratch for the suffix states;
+   *   prefix_o     [B, Hq, Dv] in q's dtype, prefix_lse float [B, Hq] (natural log, -inf = empty): the attention state of
+   *                every (request, head) over the shared prefix [0, P), computed ONCE for the batch by b200_extend_attn
+   *                (prefix_only = 1, lse_out).  `out` receives the merged result.                                      */
+  const void* kv_start;
+  void* cascade_o;
+  void* cascade_lse;
+  const void* prefix_o;
+  const void* prefix_lse;
 } b200_decode_attn_params;
 
 /* number of KV splits the kernel will use for this problem (so that the caller can size scratch) */
@@ -173,8 +185,33 @@ typedef struct b200_extend_attn_params {
   int32_t prefix_only;
   int32_t reserved0;
   void* lse_out;
+  /* optional float [T_ext, Hq, Dv]: the normalised output in fp32 INSTEAD of `out` (which may then be NULL), with the
+   * softmax weights kept exact for P V (hi + lo halves) -- the prefix state cascade decode merges, held to the decode
+   * tolerance (2e-3) rather than the extend one (1e-2). */
+  void* out_f32;
 } b200_extend_attn_params;
 int b200_extend_attn(const b200_extend_attn_params* p, void* stream);
+
+/* merge_state / merge_state_v2 (sgl-kernel/csrc/attention/cascade.cu:12-55, merge_attn_states.cu:30-120; Python wrappers
+ * sgl_kernel/attention.py:12-52): v_* [T, H, D] bf16/f16 contiguous, s_* float [T, H] natural-log LSE (an infinite value
+ * marks an empty state); v_merged = (e^{s_a} v_a + e^{s_b} v_b) / (e^{s_a} + e^{s_b}), s_merged = log(e^{s_a} + e^{s_b})
+ * (s_merged may be NULL).  D % 8 == 0. */
+int b200_merge_state(const void* v_a, const float* s_a, const void* v_b, const float* s_b, void* v_merged, float* s_merged,
+                     int64_t T, int H, int D, int dtype, void* stream);
+
+/* Length P of the page-table prefix shared by ALL B requests of a decode batch (RadixAttention gives requests with a
+ * common prompt prefix the same KV slots): the largest multiple of `align` such that req_to_token[req_b, j] is the same
+ * for every b and j < P, P <= min_b seq_len_b - 1, and 0 when that is below `min_len` or B < 2.  Stays on the device:
+ *   prefix_len  int32[1] = P  (the kv_start of b200_decode_attn);
+ *   one_seq_len int64[1] = P + B, one_req int64[1] = req_pool_indices[0]: with extend_seq_lens = [B] and
+ *   extend_start_loc = [0] they present the batch's B queries to b200_extend_attn (prefix_only) as one request whose
+ *   prefix is the shared one.
+ * scratch: int32[1] that holds INT_MAX between calls (fill it once with 0x7f bytes).  meta_i32_mask as in
+ * b200_decode_attn_params (bit 0 seq_lens, bit 1 req_pool_indices are int32).  No reference counterpart (the reference
+ * gets the prefix structure from its radix tree on the host; here the kernels stay CUDA-graph replayable). */
+int b200_shared_prefix_len(const void* req_to_token, int idx_is_i64, int64_t req_to_token_stride, const void* req_pool_indices,
+                           const void* seq_lens, int meta_i32_mask, int B, int align, int min_len, int32_t* scratch,
+                           int32_t* prefix_len, int64_t* one_seq_len, int64_t* one_req, void* stream);
 
 /* --------------------------------------------------------------------------------------------
  * Page-table index builders (integer, bit-exact), python/sglang/srt/layers/attention/utils.py

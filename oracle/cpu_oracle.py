@@ -246,3 +246,38 @@ def e4m3_to_f32(x: torch.Tensor) -> torch.Tensor:
     y = torch.empty(x.shape, dtype=torch.float32)
     lib().orc_cvt_e4m3_to_f32(_p(x), _p(y), _i64(x.numel()))
     return y
+
+
+def merge_state(v_a, s_a, v_b, s_b):
+    """merge_attn_states_kernel (sgl-kernel/csrc/attention/merge_attn_states.cu:30-120; same contract as merge_state,
+    cascade.cu:12-55; torch form in sgl-kernel/tests/test_merge_state_v2.py): states over two disjoint key sets ->
+    the state over their union.  v [T, H, D], s = natural-log LSE [T, H]; an infinite s marks an empty state."""
+    la, lb = s_a.float().clone(), s_b.float().clone()
+    la[torch.isinf(la)] = float("-inf")
+    lb[torch.isinf(lb)] = float("-inf")
+    mx = torch.maximum(la, lb)
+    ea, eb = torch.exp(la - mx), torch.exp(lb - mx)
+    den = ea + eb
+    wa, wb = ea / den, eb / den
+    dead = torch.isinf(mx)
+    wa[dead], wb[dead] = 0.0, 0.0
+    out = (v_a.float() * wa[..., None] + v_b.float() * wb[..., None]).to(v_a.dtype)
+    lse = torch.log(den) + mx
+    lse[dead] = float("-inf")
+    return out, lse
+
+
+def shared_prefix_len(req_to_token, req_pool_indices, seq_lens, align: int = 128, min_len: int = 256) -> int:
+    """Restatement of b200_shared_prefix_len (no reference counterpart: the reference knows the shared prefix from its
+    radix tree): leading page-table entries common to all requests, at most min(seq_len) - 1, rounded down to `align`."""
+    B = seq_lens.numel()
+    if B < 2:
+        return 0
+    rows = req_to_token[req_pool_indices.long()]
+    lim = int(seq_lens.min()) - 1
+    if lim <= 0:
+        return 0
+    same = (rows[:, :lim] == rows[0:1, :lim]).all(dim=0)
+    p = int(same.long().cumprod(0).sum())
+    p = p // align * align
+    return p if p >= min_len else 0

@@ -42,6 +42,7 @@ class DecodeAttnParams(C.Structure):
         ("meta_i32_mask", C.c_int32), ("page_size", C.c_int32),
         ("q_rope", c_void_p), ("qrope_stride_b", c_int64), ("qrope_stride_h", c_int64),
         ("k_rope_new", c_void_p), ("krope_stride_b", c_int64),
+        ("kv_dtype", C.c_int32), ("k_scale", c_float), ("v_scale", c_float), ("reserved1", C.c_int32),
         ("kv_start", c_void_p), ("cascade_o", c_void_p), ("cascade_lse", c_void_p), ("prefix_o", c_void_p), ("prefix_lse", c_void_p),
     ]
 
@@ -83,6 +84,9 @@ SIGNATURES = {
                                            c_float, c_float, c_float, c_void_p]),
     "b200_set_kv_buffer": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64,
                                    c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_set_kv_buffer_fp8": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64,
+                                       c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_float,
+                                       c_void_p]),
     "b200_extend_attn": (c_int, [C.POINTER(ExtendAttnParams), c_void_p]),
     "b200_merge_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "b200_shared_prefix_len": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,

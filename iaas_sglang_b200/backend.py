@@ -180,7 +180,8 @@ class B200AttnBackend(_Base):
                 key = k.view(-1, layer.tp_k_head_num, layer.qk_head_dim)
                 value = v.view(-1, layer.tp_v_head_num, layer.v_head_dim) if v is not None else None
         casc = None
-        if self.cascade and self.cascade_state is not None and q_rope is None and qv.shape[0] <= self.cascade_state.max_bs:
+        if (self.cascade and self.cascade_state is not None and q_rope is None and qv.shape[0] <= self.cascade_state.max_bs
+                and k_buf.element_size() == 2):
             casc = self.cascade_state
             casc.prefix_attention(qv, k_buf, v_buf, forward_batch.req_to_token_pool.req_to_token, layer.scaling, layer.logit_cap)
         res = ops.decode_attention(
@@ -188,7 +189,9 @@ class B200AttnBackend(_Base):
             md.attn_logits, forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             forward_batch.seq_lens, layer.scaling, layer.logit_cap,
             max_seq_len=md.max_seq_len, num_splits=md.num_kv_splits, fused_kv_write=True, quant_fp8=bool(quant_fp8),
-            q_rope=q_rope, k_rope=kr, cascade=casc)
+            q_rope=q_rope, k_rope=kr, cascade=casc,
+            k_scale=getattr(layer, "k_scale_float", None) or (float(layer.k_scale) if getattr(layer, "k_scale", None) is not None else None),
+            v_scale=getattr(layer, "v_scale_float", None) or (float(layer.v_scale) if getattr(layer, "v_scale", None) is not None else None))
         if quant_fp8:
             return res[1], res[2]
         return o

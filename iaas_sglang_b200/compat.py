@@ -99,16 +99,20 @@ class MHATokenToKVPool:
         self.v_head_dim = v_head_dim or head_dim
         self.start_layer = start_layer or 0
         self.end_layer = end_layer or layer_num - 1
-        self.k_buffer = [torch.zeros((size + page_size, head_num, head_dim), dtype=dtype, device=device)
+        # memory_pool.py:116-121: fp8 pools are stored as uint8 (index_put has no fp8) and viewed as the dtype on read
+        self.store_dtype = torch.uint8 if dtype in (torch.float8_e4m3fn, torch.float8_e5m2) else dtype
+        self.k_buffer = [torch.zeros((size + page_size, head_num, head_dim), dtype=self.store_dtype, device=device)
                          for _ in range(layer_num)]
-        self.v_buffer = [torch.zeros((size + page_size, head_num, self.v_head_dim), dtype=dtype, device=device)
+        self.v_buffer = [torch.zeros((size + page_size, head_num, self.v_head_dim), dtype=self.store_dtype, device=device)
                          for _ in range(layer_num)]
 
     def get_key_buffer(self, layer_id: int):
-        return self.k_buffer[layer_id - self.start_layer]
+        b = self.k_buffer[layer_id - self.start_layer]
+        return b.view(self.dtype) if self.store_dtype != self.dtype else b
 
     def get_value_buffer(self, layer_id: int):
-        return self.v_buffer[layer_id - self.start_layer]
+        b = self.v_buffer[layer_id - self.start_layer]
+        return b.view(self.dtype) if self.store_dtype != self.dtype else b
 
     def get_kv_buffer(self, layer_id: int):
         return self.get_key_buffer(layer_id), self.get_value_buffer(layer_id)
@@ -117,9 +121,12 @@ class MHATokenToKVPool:
         """memory_pool.py:418-456 (same-dtype branch), on our scatter kernel."""
         from . import ops
 
-        if k_scale is not None or v_scale is not None or cache_k.dtype != self.dtype:
-            raise NotImplementedError("fp8 KV cache (k_scale/v_scale) is a 'next' row (SURVEY 8f rank 4)")
         lid = layer_id_override if layer_id_override is not None else layer.layer_id
+        if cache_k.dtype != self.dtype:   # memory_pool.py:431-440: divide by the scale, cast to the cache dtype
+            if self.dtype != torch.float8_e4m3fn:
+                raise NotImplementedError("KV cache dtype cast other than bf16/f16 -> float8_e4m3fn")
+            ops.set_kv_buffer_fp8(self.get_key_buffer(lid), self.get_value_buffer(lid), loc, cache_k, cache_v, k_scale, v_scale)
+            return
         ops.set_kv_buffer(self.get_key_buffer(lid), self.get_value_buffer(lid), loc, cache_k, cache_v)
 
 

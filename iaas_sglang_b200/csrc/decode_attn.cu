@@ -75,6 +75,10 @@ struct DecodeKParams {
   int is_mla;
   float sm_scale, logit_cap;
   MergeQuant mq;
+  // FP8 KV cache (memory_pool.py:116-121,431-440; layers/quantization/kv_cache.py): the pool holds e4m3 codes,
+  // K = code * k_scale, V = code * v_scale (tuned GQA path, D = 128; strides in ELEMENTS of the pool dtype)
+  int kv_fp8;
+  float k_scale, v_scale;
   // cascade / shared-prefix decode (tuned GQA path): the kernel attends to positions [*kv_start, seq_len) only, every
   // (request, head) state goes through the merge kernel, which adds the state over the shared prefix [0, *kv_start)
   // computed once for the whole batch (extend kernel, prefix_only)
@@ -97,11 +101,11 @@ constexpr int kMaxSmem = 232448;  // 227 KB: the sm_100 per-block opt-in limit
 constexpr int kMaxBatchTable = 1024;
 constexpr int kMaxPartials = 256;  // >= launch grid of the tuned kernel (one CTA per SM)
 
-template <int D, int HPC>
+template <int D, int HPC, int EB = 2>   // EB = bytes per KV element: 2 (bf16 / f16 pool) or 1 (e4m3 pool, FP8 KV cache)
 struct AttnCfg {
   static constexpr int WT = kConsumerWarps / HPC;
   static constexpr int TILE_T = WT * kTokPerWarp;
-  static constexpr int ROW_BYTES = HPC * D * 2;
+  static constexpr int ROW_BYTES = HPC * D * EB;
   static constexpr int ROW_PITCH = ROW_BYTES + 16;
   // rows >= 1 KB go through the TMA bulk-copy engine (one UBLKCP per row); shorter rows (few KV heads per
   // GPU under TP) are limited by the per-copy cost of that engine (measured: 256 B rows -> 47 % of HBM), so
@@ -172,9 +176,26 @@ struct SegCursor {
   }
 };
 
-template <int D, int HPC, bool BF16>
+// two e4m3 codes (low / high 16 bits of `w`) -> packed f16x2, exact
+__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t w, bool hi) {
+  uint32_t r;
+  const uint16_t h = (uint16_t)(hi ? (w >> 16) : (w & 0xffffu));
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"(h));
+  return r;
+}
+// bf16 / f16 pair -> f16x2 (Q for the FP8-KV path: the MMAs run in f16)
+template <bool BF16>
+__device__ __forceinline__ uint32_t to_f16x2(uint32_t w) {
+  if constexpr (!BF16) return w;
+  const float2 f = unpack_half2<true>(w);
+  return pack_half2<false>(f.x, f.y);
+}
+
+template <int D, int HPC, bool BF16, bool KV8 = false>
 __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const __grid_constant__ DecodeKParams p) {
-  using C = AttnCfg<D, HPC>;
+  constexpr int EB = KV8 ? 1 : 2;
+  using C = AttnCfg<D, HPC, EB>;
+  constexpr bool MB = KV8 ? false : BF16;   // MMA operand type: e4m3 converts exactly to f16, so FP8 KV runs f16 MMAs
   constexpr int Dv = D;
   extern __shared__ __align__(128) uint8_t smem[];
   int64_t* s_loc = reinterpret_cast<int64_t*>(smem + C::RING_BYTES);
@@ -301,8 +322,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
               const int64_t idx = p.idx64 ? (((int64_t)hi[r] << 32) | (uint32_t)lo[r]) : (int64_t)lo[r];
               const int row = pw * RW + (item >> 1);
               const bool is_v = item & 1;
-              const uint16_t* src = is_v ? p.v_buf + idx * p.vb_st + kvh0 * p.vb_sh : p.k_buf + idx * p.kb_st + kvh0 * p.kb_sh;
-              if (idx == loc_b) src = is_v ? vnew_row : knew_row;
+              const void* src = is_v ? (const void*)(reinterpret_cast<const uint8_t*>(p.v_buf) + (idx * p.vb_st + kvh0 * p.vb_sh) * EB)
+                                     : (const void*)(reinterpret_cast<const uint8_t*>(p.k_buf) + (idx * p.kb_st + kvh0 * p.kb_sh) * EB);
+              if (!KV8 && idx == loc_b) src = is_v ? vnew_row : knew_row;
               bulk_g2s(kdst + (is_v ? C::KV_BYTES : 0) + row * C::ROW_PITCH, src, C::ROW_BYTES, &full[s]);
             }
           }
@@ -336,10 +358,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
         // up one-to-one in the kernel time), so the loop is kept to a shuffle, two 32 x 32 -> 64-bit multiply-adds and
         // the two copies per pair of rows: int32 page-table entries (the usual req_to_token dtype) with byte strides
         // that fit 32 bits; the new token's substitution is only looked for in the tile that can hold it.
-        const bool fast32 = !p.idx64 && p.kb_st * 2 < (int64_t)1 << 31 && p.vb_st * 2 < (int64_t)1 << 31;
-        const uint32_t kst_b = (uint32_t)(p.kb_st * 2), vst_b = (uint32_t)(p.vb_st * 2);
-        const char* kbase = reinterpret_cast<const char*>(p.k_buf + kvh0 * p.kb_sh) + chunk * 16;
-        const char* vbase = reinterpret_cast<const char*>(p.v_buf + kvh0 * p.vb_sh) + chunk * 16;
+        const bool fast32 = !p.idx64 && p.kb_st * EB < (int64_t)1 << 31 && p.vb_st * EB < (int64_t)1 << 31;
+        const uint32_t kst_b = (uint32_t)(p.kb_st * EB), vst_b = (uint32_t)(p.vb_st * EB);
+        const char* kbase = reinterpret_cast<const char*>(p.k_buf) + kvh0 * p.kb_sh * EB + chunk * 16;
+        const char* vbase = reinterpret_cast<const char*>(p.v_buf) + kvh0 * p.vb_sh * EB + chunk * 16;
         const bool unit_tail = p.fused_new && cur.tile + n == cur.tiles_b;   // the segment ends at the request's last token
         for (int it = 0; it < n; ++it, ++gt) {
           const int s = gt % C::STAGES;
@@ -367,14 +389,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
 #pragma unroll 4
             for (int r = 0; r < RW; r += RPI) {
               const int64_t ri = __shfl_sync(0xffffffffu, idx, r + sub);
-              const uint16_t* ks = p.k_buf + ri * p.kb_st + kvh0 * p.kb_sh;
-              const uint16_t* vs = p.v_buf + ri * p.vb_st + kvh0 * p.vb_sh;
-              if (ri == loc_b) {
-                ks = knew_row;
-                vs = vnew_row;
+              const char* ks = reinterpret_cast<const char*>(p.k_buf) + (ri * p.kb_st + kvh0 * p.kb_sh) * EB;
+              const char* vs = reinterpret_cast<const char*>(p.v_buf) + (ri * p.vb_st + kvh0 * p.vb_sh) * EB;
+              if (!KV8 && ri == loc_b) {
+                ks = reinterpret_cast<const char*>(knew_row);
+                vs = reinterpret_cast<const char*>(vnew_row);
               }
-              cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 8);
-              cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 8);
+              cp_async_16(kdst + r * C::ROW_PITCH, ks + chunk * 16);
+              cp_async_16(kdst + C::KV_BYTES + r * C::ROW_PITCH, vs + chunk * 16);
             }
           }
           cp_async_mbar_arrive_noinc(&full[s]);
@@ -391,7 +413,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
   const int wh = warp / C::WT, wt = warp - wh * C::WT;
   const int g = lane >> 2, t = lane & 3;
   const bool has_cap = p.logit_cap > 0.f;
-  const float scale2 = p.sm_scale * kLog2e;
+  const float sm_scale_k = KV8 ? p.sm_scale * p.k_scale : p.sm_scale;   // logits = q . (code * k_scale)
+  const float scale2 = sm_scale_k * kLog2e;
   const int lm = lane >> 3, lr = lane & 7;
   // ldmatrix lane addressing: K non-transposed, V transposed
   const uint32_t k_lane_off = (uint32_t)(((lm >> 1) * 8 + lr) * C::ROW_PITCH + (lm & 1) * 16);
@@ -420,10 +443,21 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       const bool v0 = g < rows_valid, v1 = g + 8 < rows_valid;
 #pragma unroll
       for (int ks = 0; ks < D / 16; ++ks) {
-        qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16) : 0u;
-        qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16) : 0u;
-        qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 8) : 0u;
-        qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 8) : 0u;
+        if constexpr (KV8) {
+          // One ldmatrix of e4m3 rows hands thread (g, t) the four codes k = 16 ks + 4 t .. + 3 of a key, so the MMA's
+          // k-slots (2t, 2t+1 | 2t+8, 2t+9) carry k = (4t, 4t+1 | 4t+2, 4t+3): Q is loaded in the same permutation.
+          const uint16_t* a0 = p.q + b * p.q_sb + (int64_t)(qh0 + g) * p.q_sh + ks * 16 + 4 * t;
+          const uint16_t* a1 = a0 + 8 * p.q_sh;
+          qf[ks][0] = v0 ? to_f16x2<BF16>(*reinterpret_cast<const uint32_t*>(a0)) : 0u;
+          qf[ks][1] = v1 ? to_f16x2<BF16>(*reinterpret_cast<const uint32_t*>(a1)) : 0u;
+          qf[ks][2] = v0 ? to_f16x2<BF16>(*reinterpret_cast<const uint32_t*>(a0 + 2)) : 0u;
+          qf[ks][3] = v1 ? to_f16x2<BF16>(*reinterpret_cast<const uint32_t*>(a1 + 2)) : 0u;
+        } else {
+          qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16) : 0u;
+          qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16) : 0u;
+          qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 8) : 0u;
+          qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 8) : 0u;
+        }
       }
     }
     float o[Dv / 8][4];
@@ -437,16 +471,29 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       const uint32_t ph = (gt / C::STAGES) & 1;
       s_last = s;
       mbar_wait(&full[s], ph);
-      const uint32_t kbase = smem_base + s * C::STAGE_BYTES + (wt * kTokPerWarp) * C::ROW_PITCH + wh * D * 2;
+      const uint32_t kbase = smem_base + s * C::STAGE_BYTES + (wt * kTokPerWarp) * C::ROW_PITCH + wh * D * EB;
       const uint32_t vbase = kbase + C::KV_BYTES;
 
       float sc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+      if constexpr (KV8) {
+        // 32 bytes of a key row = 32 k: matrices (keys 0-7 | 8-15) x (k 0-15 | 16-31); a register = four codes
 #pragma unroll
-      for (int ks = 0; ks < D / 16; ++ks) {
-        uint32_t r0, r1, r2, r3;
-        ldsm_x4(kbase + k_lane_off + ks * 32, r0, r1, r2, r3);
-        mma_16816<BF16>(sc[0], qf[ks], r0, r1);
-        mma_16816<BF16>(sc[1], qf[ks], r2, r3);
+        for (int kq = 0; kq < D / 32; ++kq) {
+          uint32_t r0, r1, r2, r3;
+          ldsm_x4(kbase + k_lane_off + kq * 32, r0, r1, r2, r3);
+          mma_16816<false>(sc[0], qf[2 * kq], e4m3x2_to_f16x2(r0, false), e4m3x2_to_f16x2(r0, true));
+          mma_16816<false>(sc[0], qf[2 * kq + 1], e4m3x2_to_f16x2(r1, false), e4m3x2_to_f16x2(r1, true));
+          mma_16816<false>(sc[1], qf[2 * kq], e4m3x2_to_f16x2(r2, false), e4m3x2_to_f16x2(r2, true));
+          mma_16816<false>(sc[1], qf[2 * kq + 1], e4m3x2_to_f16x2(r3, false), e4m3x2_to_f16x2(r3, true));
+        }
+      } else {
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+          uint32_t r0, r1, r2, r3;
+          ldsm_x4(kbase + k_lane_off + ks * 32, r0, r1, r2, r3);
+          mma_16816<BF16>(sc[0], qf[ks], r0, r1);
+          mma_16816<BF16>(sc[1], qf[ks], r2, r3);
+        }
       }
       const int64_t tok0 = kv0 + (int64_t)it * C::TILE_T + wt * kTokPerWarp;
       float mx[2] = {-INFINITY, -INFINITY};
@@ -456,7 +503,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
         for (int e = 0; e < 4; ++e) {
           float v = sc[nt][e];
           if (has_cap) {
-            v *= p.sm_scale;
+            v *= sm_scale_k;
             v = p.logit_cap * tanhf(v / p.logit_cap) * kLog2e;
           } else {
             v *= scale2;
@@ -485,11 +532,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
       for (int nt = 0; nt < 2; ++nt) {
         const float p0 = exp2f(sc[nt][0] - m_use[0]), p1 = exp2f(sc[nt][1] - m_use[0]);
         const float p2 = exp2f(sc[nt][2] - m_use[1]), p3 = exp2f(sc[nt][3] - m_use[1]);
-        pa[nt * 2 + 0] = pack_half2<BF16>(p0, p1);
-        pa[nt * 2 + 1] = pack_half2<BF16>(p2, p3);
-        const float2 h01 = unpack_half2<BF16>(pa[nt * 2 + 0]), h23 = unpack_half2<BF16>(pa[nt * 2 + 1]);
-        pb[nt * 2 + 0] = pack_half2<BF16>(p0 - h01.x, p1 - h01.y);
-        pb[nt * 2 + 1] = pack_half2<BF16>(p2 - h23.x, p3 - h23.y);
+        pa[nt * 2 + 0] = pack_half2<MB>(p0, p1);
+        pa[nt * 2 + 1] = pack_half2<MB>(p2, p3);
+        const float2 h01 = unpack_half2<MB>(pa[nt * 2 + 0]), h23 = unpack_half2<MB>(pa[nt * 2 + 1]);
+        pb[nt * 2 + 0] = pack_half2<MB>(p0 - h01.x, p1 - h01.y);
+        pb[nt * 2 + 1] = pack_half2<MB>(p2 - h23.x, p3 - h23.y);
         ps[0] += p0 + p1;
         ps[1] += p2 + p3;
       }
@@ -504,14 +551,38 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
           o[j][3] *= alpha[1];
         }
       }
+      if constexpr (KV8) {
+        // 32 bytes of the value rows = 32 columns.  The transposing ldmatrix moves byte PAIRS: thread (g, t) receives
+        // the codes V[tok 2t | 2t+1][col 2g | 2g+1]; a byte permute separates the even and the odd column, each goes
+        // through its own MMA, and the thread ends up owning the four adjacent columns 16 q + 4 t .. + 3 of block q:
+        // o[2q] holds columns +0 / +2 (c0 / c1), o[2q+1] columns +1 / +3 (the scratch write below knows).
 #pragma unroll
-      for (int jp = 0; jp < Dv / 16; ++jp) {
-        uint32_t r0, r1, r2, r3;
-        ldsm_x4_t(vbase + v_lane_off + jp * 32, r0, r1, r2, r3);
-        mma_16816<BF16>(o[2 * jp], pa, r0, r1);
-        mma_16816<BF16>(o[2 * jp + 1], pa, r2, r3);
-        mma_16816<BF16>(o[2 * jp], pb, r0, r1);
-        mma_16816<BF16>(o[2 * jp + 1], pb, r2, r3);
+        for (int jq = 0; jq < Dv / 32; ++jq) {
+          uint32_t r0, r1, r2, r3;
+          ldsm_x4_t(vbase + v_lane_off + jq * 32, r0, r1, r2, r3);
+          uint32_t be0 = e4m3x2_to_f16x2(__byte_perm(r0, 0, 0x4420), false), be1 = e4m3x2_to_f16x2(__byte_perm(r1, 0, 0x4420), false);
+          uint32_t bo0 = e4m3x2_to_f16x2(__byte_perm(r0, 0, 0x4431), false), bo1 = e4m3x2_to_f16x2(__byte_perm(r1, 0, 0x4431), false);
+          mma_16816<false>(o[4 * jq], pa, be0, be1);
+          mma_16816<false>(o[4 * jq + 1], pa, bo0, bo1);
+          mma_16816<false>(o[4 * jq], pb, be0, be1);
+          mma_16816<false>(o[4 * jq + 1], pb, bo0, bo1);
+          be0 = e4m3x2_to_f16x2(__byte_perm(r2, 0, 0x4420), false); be1 = e4m3x2_to_f16x2(__byte_perm(r3, 0, 0x4420), false);
+          bo0 = e4m3x2_to_f16x2(__byte_perm(r2, 0, 0x4431), false); bo1 = e4m3x2_to_f16x2(__byte_perm(r3, 0, 0x4431), false);
+          mma_16816<false>(o[4 * jq + 2], pa, be0, be1);
+          mma_16816<false>(o[4 * jq + 3], pa, bo0, bo1);
+          mma_16816<false>(o[4 * jq + 2], pb, be0, be1);
+          mma_16816<false>(o[4 * jq + 3], pb, bo0, bo1);
+        }
+      } else {
+#pragma unroll
+        for (int jp = 0; jp < Dv / 16; ++jp) {
+          uint32_t r0, r1, r2, r3;
+          ldsm_x4_t(vbase + v_lane_off + jp * 32, r0, r1, r2, r3);
+          mma_16816<BF16>(o[2 * jp], pa, r0, r1);
+          mma_16816<BF16>(o[2 * jp + 1], pa, r2, r3);
+          mma_16816<BF16>(o[2 * jp], pb, r0, r1);
+          mma_16816<BF16>(o[2 * jp + 1], pb, r2, r3);
+        }
       }
       if (it + 1 < n) {  // the segment's last stage is released after it has served as merge scratch
         __syncwarp();
@@ -531,10 +602,22 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
     float* scratch = reinterpret_cast<float*>(smem + s_last * C::STAGE_BYTES);  // [warp][16][Dv + 2]
     {
       float* my = scratch + (size_t)warp * 16 * (Dv + 2);
+      if constexpr (KV8) {   // columns 16 q + 4 t .. + 3: (even tile c0, odd tile c0, even tile c1, odd tile c1)
 #pragma unroll
-      for (int j = 0; j < Dv / 8; ++j) {
-        *reinterpret_cast<float2*>(my + g * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
-        *reinterpret_cast<float2*>(my + (g + 8) * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][2], o[j][3]);
+        for (int q = 0; q < Dv / 16; ++q) {
+          float* d0 = my + g * (Dv + 2) + q * 16 + 4 * t;
+          float* d1 = my + (g + 8) * (Dv + 2) + q * 16 + 4 * t;
+          *reinterpret_cast<float2*>(d0) = make_float2(o[2 * q][0], o[2 * q + 1][0]);
+          *reinterpret_cast<float2*>(d0 + 2) = make_float2(o[2 * q][1], o[2 * q + 1][1]);
+          *reinterpret_cast<float2*>(d1) = make_float2(o[2 * q][2], o[2 * q + 1][2]);
+          *reinterpret_cast<float2*>(d1 + 2) = make_float2(o[2 * q][3], o[2 * q + 1][3]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < Dv / 8; ++j) {
+          *reinterpret_cast<float2*>(my + g * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
+          *reinterpret_cast<float2*>(my + (g + 8) * (Dv + 2) + j * 8 + 2 * t) = make_float2(o[j][2], o[j][3]);
+        }
       }
       if (t == 0) {
         my[g * (Dv + 2) + Dv] = m_run[0];
@@ -564,7 +647,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
         L += bw[Dv + 1] * sc_w;
         O += bw[dv] * sc_w;
       }
-      const float inv = L > 0.f ? 1.f / L : 0.f;
+      const float inv = (L > 0.f ? 1.f / L : 0.f) * (KV8 ? p.v_scale : 1.f);   // V = code * v_scale
       if (whole_unit) {
         const int head = (kvh0 + h) * p.G + row0 + r;
         if (p.casc_o) {   // cascade: the merge kernel still has to add the shared-prefix state -> fp32 state, not the output
@@ -936,6 +1019,25 @@ __global__ void set_kv_kernel(uint16_t* k_buf, int64_t kb_st, int64_t kb_sh, uin
   }
 }
 
+// FP8 KV cache append (memory_pool.py:431-440: cache_k.div_(k_scale); cache_k.to(float8_e4m3fn); store as uint8):
+// code = e4m3(x / scale), round to nearest even, saturating -- what torch's .to(float8_e4m3fn) does for finite values in
+// range (the oracle restates it).  grid (B, Hkv), strides of the pool in bytes (= elements).
+template <bool BF16>
+__global__ void set_kv_fp8_kernel(uint8_t* k_buf, int64_t kb_st, int64_t kb_sh, uint8_t* v_buf, int64_t vb_st, int64_t vb_sh,
+                                  const uint16_t* k_new, int64_t kn_sb, int64_t kn_sh, const uint16_t* v_new, int64_t vn_sb,
+                                  int64_t vn_sh, const void* loc, int loc32, int D, int Dv, float k_scale, float v_scale) {
+  const int b = blockIdx.x, h = blockIdx.y;
+  const int64_t l = meta_at(loc, b, loc32);
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    const float x = __fdiv_rn(half_to_float<BF16>(k_new[b * kn_sb + h * kn_sh + i]), k_scale);
+    k_buf[l * kb_st + h * kb_sh + i] = (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
+  }
+  for (int i = threadIdx.x; i < Dv; i += blockDim.x) {
+    const float x = __fdiv_rn(half_to_float<BF16>(v_new[b * vn_sb + h * vn_sh + i]), v_scale);
+    v_buf[l * vb_st + h * vb_sh + i] = (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -954,10 +1056,10 @@ static int attn_grid() {
   return g > kMaxPartials ? kMaxPartials : g;
 }
 
-template <int D, int HPC, bool BF16>
+template <int D, int HPC, bool BF16, bool KV8 = false>
 static int launch_mma(const DecodeKParams& kp, cudaStream_t st) {
-  using C = AttnCfg<D, HPC>;
-  auto kern = decode_attn_mma_kernel<D, HPC, BF16>;
+  using C = AttnCfg<D, HPC, KV8 ? 1 : 2>;
+  auto kern = decode_attn_mma_kernel<D, HPC, BF16, KV8>;
   static bool configured = false;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
@@ -978,6 +1080,17 @@ static int dispatch_mma(const DecodeKParams& kp, int hpc, cudaStream_t st) {
   B200_CASE(64, 8) B200_CASE(64, 4) B200_CASE(64, 2) B200_CASE(64, 1)
 #undef B200_CASE
   set_error("decode_attn: no mma instantiation for D=%d hpc=%d", kp.D, hpc);
+  return B200_ERR_UNSUPPORTED;
+}
+
+// FP8 KV cache: D = 128 only (Llama / Qwen head size)
+template <bool BF16>
+static int dispatch_mma_kv8(const DecodeKParams& kp, int hpc, cudaStream_t st) {
+  if (kp.D == 128 && hpc == 8) return launch_mma<128, 8, BF16, true>(kp, st);
+  if (kp.D == 128 && hpc == 4) return launch_mma<128, 4, BF16, true>(kp, st);
+  if (kp.D == 128 && hpc == 2) return launch_mma<128, 2, BF16, true>(kp, st);
+  if (kp.D == 128 && hpc == 1) return launch_mma<128, 1, BF16, true>(kp, st);
+  set_error("decode_attn: the FP8 KV path needs head_dim 128 (got %d)", kp.D);
   return B200_ERR_UNSUPPORTED;
 }
 
@@ -1038,6 +1151,23 @@ extern "C" int b200_set_kv_buffer(void* k_buf, int64_t kb_st, int64_t kb_sh, voi
   return launched("set_kv_kernel launch");
 }
 
+extern "C" int b200_set_kv_buffer_fp8(void* k_buf, int64_t kb_st, int64_t kb_sh, void* v_buf, int64_t vb_st, int64_t vb_sh,
+                                      const void* k_new, int64_t kn_sb, int64_t kn_sh, const void* v_new, int64_t vn_sb,
+                                      int64_t vn_sh, const int64_t* loc, int B, int Hkv, int D, int Dv, int src_dtype,
+                                      float k_scale, float v_scale, void* stream) {
+  B200_REQUIRE(k_buf && v_buf && k_new && v_new && loc && B >= 0 && Hkv > 0 && D > 0 && Dv > 0, B200_ERR_ARG, "set_kv_buffer_fp8: bad argument");
+  B200_REQUIRE(src_dtype == B200_BF16 || src_dtype == B200_F16, B200_ERR_UNSUPPORTED, "set_kv_buffer_fp8: source must be bf16/f16");
+  if (B == 0) return B200_OK;
+  const float ks = k_scale > 0.f ? k_scale : 1.f, vs = v_scale > 0.f ? v_scale : 1.f;
+  if (src_dtype == B200_BF16)
+    set_kv_fp8_kernel<true><<<dim3(B, Hkv), 128, 0, (cudaStream_t)stream>>>((uint8_t*)k_buf, kb_st, kb_sh, (uint8_t*)v_buf, vb_st, vb_sh,
+        (const uint16_t*)k_new, kn_sb, kn_sh, (const uint16_t*)v_new, vn_sb, vn_sh, loc, 0, D, Dv, ks, vs);
+  else
+    set_kv_fp8_kernel<false><<<dim3(B, Hkv), 128, 0, (cudaStream_t)stream>>>((uint8_t*)k_buf, kb_st, kb_sh, (uint8_t*)v_buf, vb_st, vb_sh,
+        (const uint16_t*)k_new, kn_sb, kn_sh, (const uint16_t*)v_new, vn_sb, vn_sh, loc, 0, D, Dv, ks, vs);
+  return launched("set_kv_fp8_kernel launch");
+}
+
 static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* mq, void* stream) {
   B200_REQUIRE(a != nullptr, B200_ERR_ARG, "decode_attn: null params");
   B200_REQUIRE(a->B >= 0 && a->Hq > 0 && a->Hkv > 0 && a->D > 0 && a->Dv > 0, B200_ERR_ARG, "decode_attn: bad sizes");
@@ -1080,6 +1210,10 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
   kp.kv_start = (const int32_t*)a->kv_start;
   kp.casc_o = (float*)a->cascade_o; kp.casc_lse = (float*)a->cascade_lse;
   kp.pre_o = (const float*)a->prefix_o; kp.pre_lse = (const float*)a->prefix_lse;
+  kp.kv_fp8 = a->kv_dtype == B200_KV_E4M3 ? 1 : 0;
+  kp.k_scale = a->k_scale > 0.f ? a->k_scale : 1.f;
+  kp.v_scale = a->v_scale > 0.f ? a->v_scale : 1.f;
+  B200_REQUIRE(a->kv_dtype == 0 || a->kv_dtype == B200_KV_E4M3, B200_ERR_ARG, "decode_attn: kv_dtype must be 0 (q's dtype) or B200_KV_E4M3");
   const bool cascade = a->kv_start || a->cascade_o || a->cascade_lse || a->prefix_o || a->prefix_lse;
   B200_REQUIRE(!cascade || (a->kv_start && a->cascade_o && a->cascade_lse && a->prefix_o && a->prefix_lse), B200_ERR_ARG,
                "decode_attn: cascade needs kv_start, cascade_o, cascade_lse, prefix_o and prefix_lse together");
@@ -1089,8 +1223,9 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
   int hpc = pick_hpc(a->Hkv);
   if (mma) {
     auto al16 = [](const void* p) { return ((uintptr_t)p & 15) == 0; };
-    const bool rows_ok = al16(a->k_buf) && al16(a->v_buf) && a->kbuf_stride_t % 8 == 0 && a->vbuf_stride_t % 8 == 0 &&
-                         a->kbuf_stride_h % 8 == 0 && a->vbuf_stride_h % 8 == 0;
+    const int am = a->kv_dtype == B200_KV_E4M3 ? 16 : 8;   // elements per 16 bytes of the pool
+    const bool rows_ok = al16(a->k_buf) && al16(a->v_buf) && a->kbuf_stride_t % am == 0 && a->vbuf_stride_t % am == 0 &&
+                         a->kbuf_stride_h % am == 0 && a->vbuf_stride_h % am == 0;
     const bool q_ok = ((uintptr_t)a->q & 3) == 0 && a->q_stride_b % 2 == 0 && a->q_stride_h % 2 == 0;
     if (!rows_ok || !q_ok) mma = false;
     if (mma && hpc > 1 && (a->kbuf_stride_h != a->D || a->vbuf_stride_h != a->Dv)) hpc = 1;  // heads not adjacent
@@ -1127,7 +1262,23 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
                         (hpc == 1 || (a->knew_stride_h == a->D && a->vnew_stride_h == a->Dv));
     if (!new_ok) fused = false;
   }
-  if (write_kv && !fused) {
+  if (kp.kv_fp8) {
+    // e4m3 pool: tuned GQA kernel with head_dim 128 only; the append is its own (quantising) launch
+    B200_REQUIRE(mma && !is_mla && a->D == 128 && !cascade, B200_ERR_UNSUPPORTED,
+                 "decode_attn: the FP8 KV cache needs the tuned GQA kernel with head_dim 128 (D=%d Dv=%d), no cascade", a->D, a->Dv);
+    fused = false;
+    if (write_kv) {
+      if (a->dtype == B200_BF16)
+        set_kv_fp8_kernel<true><<<dim3(a->B, a->Hkv), 128, 0, st>>>((uint8_t*)a->k_buf, a->kbuf_stride_t, a->kbuf_stride_h, (uint8_t*)a->v_buf,
+            a->vbuf_stride_t, a->vbuf_stride_h, (const uint16_t*)a->k_new, a->knew_stride_b, a->knew_stride_h, (const uint16_t*)a->v_new,
+            a->vnew_stride_b, a->vnew_stride_h, a->out_cache_loc, (a->meta_i32_mask >> 2) & 1, a->D, a->Dv, kp.k_scale, kp.v_scale);
+      else
+        set_kv_fp8_kernel<false><<<dim3(a->B, a->Hkv), 128, 0, st>>>((uint8_t*)a->k_buf, a->kbuf_stride_t, a->kbuf_stride_h, (uint8_t*)a->v_buf,
+            a->vbuf_stride_t, a->vbuf_stride_h, (const uint16_t*)a->k_new, a->knew_stride_b, a->knew_stride_h, (const uint16_t*)a->v_new,
+            a->vnew_stride_b, a->vnew_stride_h, a->out_cache_loc, (a->meta_i32_mask >> 2) & 1, a->D, a->Dv, kp.k_scale, kp.v_scale);
+      if (int rc = launched("set_kv_fp8_kernel launch")) return rc;
+    }
+  } else if (write_kv && !fused) {
     set_kv_kernel<<<dim3(a->B, a->Hkv), 128, 0, st>>>(
         (uint16_t*)a->k_buf, a->kbuf_stride_t, a->kbuf_stride_h, (uint16_t*)a->v_buf, a->vbuf_stride_t, a->vbuf_stride_h,
         (const uint16_t*)a->k_new, a->knew_stride_b, a->knew_stride_h, is_mla ? nullptr : (const uint16_t*)a->v_new,
@@ -1188,7 +1339,8 @@ static int decode_attn_impl(const b200_decode_attn_params* a, const MergeQuant* 
         c.mq.q = kp.mq.q + (int64_t)b0 * kp.mq.q_sm;
         c.mq.s = kp.mq.s + (int64_t)b0 * kp.mq.s_sm;
       }
-      const int rc = a->dtype == B200_BF16 ? dispatch_mma<true>(c, hpc, st) : dispatch_mma<false>(c, hpc, st);
+      const int rc = kp.kv_fp8 ? (a->dtype == B200_BF16 ? dispatch_mma_kv8<true>(c, hpc, st) : dispatch_mma_kv8<false>(c, hpc, st))
+                               : (a->dtype == B200_BF16 ? dispatch_mma<true>(c, hpc, st) : dispatch_mma<false>(c, hpc, st));
       if (rc != 0) return rc;
     }
     return B200_OK;

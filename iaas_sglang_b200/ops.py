@@ -300,7 +300,8 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
                      seq_lens, sm_scale: float, logit_cap: float, *, max_seq_len: int = 0, num_splits: int = 0,
                      fused_kv_write: bool = False, quant_fp8: bool = False, quant_eps: float = 1e-10,
                      q_rope: Optional[torch.Tensor] = None, k_rope: Optional[torch.Tensor] = None, page_size: int = 1,
-                     cascade: Optional["CascadeState"] = None):
+                     cascade: Optional["CascadeState"] = None, k_scale: Optional[float] = None,
+                     v_scale: Optional[float] = None):
     """Same positional signature as torch.ops.sgl_kernel.decode_attention_cpu (decode.cpp:1375-1388;
     schema torch_extension_cpu.cpp:264-268) on CUDA tensors.
 
@@ -314,6 +315,9 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     allocates them (cuda_graph_runner.py:273-276); req_pool_indices=None means request b owns row b of the table.
     MLA extras (cutlass_mla_backend.py:226-285): q_rope [B,Hq,64] with query = q_nope [B,Hq,512]; k_rope [B,1,64] with
     key = the latent part [B,1,512] (set_mla_kv_buffer); page_size P > 1: req_to_token is a [B, pages] page table.
+    FP8 KV cache (memory_pool.py:116-121,431-440): k_cache / v_cache of dtype float8_e4m3fn (or the pool's uint8 storage
+    with k_scale / v_scale given) hold e4m3 codes, K = code * k_scale, V = code * v_scale; key / value stay in query's dtype
+    and are appended as e4m3(x / scale).  Tuned GQA kernel, head_dim 128 (NotImplementedError otherwise).
     cascade: a CascadeState (shared_prefix_len + the prefix state of this layer): the kernel attends to the positions
     after the shared prefix only and its merge adds the prefix state -- same result, the shared KV rows are read once.
     quant_fp8=True also returns (x_q, x_s) = per_token_group_quant_fp8(output.view(B, Hq*Dv), 128,
@@ -336,7 +340,11 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
         raise RuntimeError("k_cache / v_cache shapes do not match query")
     if tuple(output.shape) != (B, Hq, Dv) or not output.is_contiguous():
         raise RuntimeError("output must be a contiguous [B, Hq, Dv] tensor")
-    if not (query.dtype == k_cache.dtype == v_cache.dtype == output.dtype) or query.dtype not in DTYPE_CODE:
+    kv_fp8 = k_cache.dtype == torch.float8_e4m3fn or (k_cache.dtype == torch.uint8 and k_scale is not None)
+    if kv_fp8:
+        if v_cache.dtype != k_cache.dtype or query.dtype != output.dtype or query.dtype not in DTYPE_CODE or query.dtype == torch.float32:
+            raise RuntimeError("fp8 KV cache: k_cache / v_cache must both be e4m3, query / output bf16 or f16")
+    elif not (query.dtype == k_cache.dtype == v_cache.dtype == output.dtype) or query.dtype not in DTYPE_CODE:
         raise RuntimeError("query, k_cache, v_cache, output must share a bf16/f16 dtype")
     if req_to_token.dtype not in (torch.int32, torch.int64) or req_to_token.stride(1) != 1:
         raise RuntimeError("req_to_token must be int32/int64 with contiguous rows")  # decode.cpp:1441-1445
@@ -385,6 +393,10 @@ def decode_attention(query, k_cache, v_cache, output, key, value, loc, attn_logi
     p.write_kv = write_kv
     p.max_seq_len = int(max_seq_len)
     p.sm_scale, p.logit_cap = float(sm_scale), float(logit_cap)
+    if kv_fp8:
+        p.kv_dtype = 3   # B200_KV_E4M3
+        p.k_scale = float(k_scale) if k_scale is not None else 1.0
+        p.v_scale = float(v_scale) if v_scale is not None else 1.0
     if cascade is not None:
         cascade.bind(p, B, Hq, Dv, query.dtype)
     S = lib.b200_decode_attn_num_splits(B, Hq, Hkv, D, Dv, int(max_seq_len), int(num_splits)) if B > 0 else 1
@@ -592,6 +604,25 @@ def set_kv_buffer(k_buffer, v_buffer, loc, cache_k, cache_v) -> None:
             ptr(ck), ck.stride(0), ck.stride(1), ptr(cv), cv.stride(0) if cv is not None else 0,
             cv.stride(1) if cv is not None else 0, ptr(loc), B, k_buffer.shape[1], k_buffer.shape[2], v_buffer.shape[2],
             k_buffer.element_size(), current_stream(dev)))
+
+
+def set_kv_buffer_fp8(k_buffer, v_buffer, loc, cache_k, cache_v, k_scale: Optional[float] = None,
+                      v_scale: Optional[float] = None) -> None:
+    """KVCache.set_kv_buffer into an FP8 pool (memory_pool.py:431-455): buffer[loc] = e4m3(cache / scale).
+    k_buffer / v_buffer: float8_e4m3fn (or the uint8 storage) [T, Hkv, D]; cache_k / cache_v: bf16 / f16."""
+    dev = require_cuda(k_buffer, v_buffer, loc, cache_k, cache_v)
+    if k_buffer.element_size() != 1 or cache_k.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("set_kv_buffer_fp8: an 8-bit pool and bf16/f16 rows are required")
+    loc = _i64(loc)
+    B = loc.numel()
+    ck = cache_k.view(B, k_buffer.shape[1], k_buffer.shape[2])
+    cv = cache_v.view(B, v_buffer.shape[1], v_buffer.shape[2])
+    with torch.cuda.device(dev):
+        check(load().b200_set_kv_buffer_fp8(
+            ptr(k_buffer), k_buffer.stride(0), k_buffer.stride(1), ptr(v_buffer), v_buffer.stride(0), v_buffer.stride(1),
+            ptr(ck), ck.stride(0), ck.stride(1), ptr(cv), cv.stride(0), cv.stride(1), ptr(loc), B, k_buffer.shape[1],
+            k_buffer.shape[2], v_buffer.shape[2], DTYPE_CODE[cache_k.dtype], float(k_scale or 1.0), float(v_scale or 1.0),
+            current_stream(dev)))
 
 
 # ---------------------------------------------------------------------------------------------

@@ -41,6 +41,7 @@ extern "C" {
 #define B200_F32 2
 
 #define B200_SGL_ABI_VERSION 3
+#define B200_KV_E4M3 3   /* b200_decode_attn_params.kv_dtype */
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -121,6 +122,13 @@ typedef struct b200_decode_attn_params {
    *   prefix_o     [B, Hq, Dv] in q's dtype, prefix_lse float [B, Hq] (natural log, -inf = empty): the attention state of
    *                every (request, head) over the shared prefix [0, P), computed ONCE for the batch by b200_extend_attn
    *                (prefix_only = 1, lse_out).  `out` receives the merged result.                                      */
+  /* FP8 KV cache (--kv-cache-dtype fp8_e4m3: memory_pool.py:116-121,431-440; layers/quantization/kv_cache.py):
+   * kv_dtype = B200_KV_E4M3: k_buf / v_buf hold e4m3 codes (the pool's uint8 storage; strides in elements = bytes),
+   * K = code * k_scale, V = code * v_scale (scale <= 0 means 1); k_new / v_new stay in q's dtype and are appended as
+   * e4m3(x / scale).  Tuned GQA kernel with head_dim 128 only (B200_ERR_UNSUPPORTED otherwise), not with cascade. */
+  int32_t kv_dtype;
+  float k_scale, v_scale;
+  int32_t reserved1;
   const void* kv_start;
   void* cascade_o;
   void* cascade_lse;
@@ -145,6 +153,13 @@ int b200_set_kv_buffer(void* k_buf, int64_t kbuf_stride_t, int64_t kbuf_stride_h
                        int64_t vbuf_stride_h, const void* k_new, int64_t knew_stride_b, int64_t knew_stride_h,
                        const void* v_new, int64_t vnew_stride_b, int64_t vnew_stride_h, const int64_t* loc, int B,
                        int Hkv, int D, int Dv, int elem_bytes, void* stream);
+
+/* The same into an FP8 (e4m3) pool: code = e4m3(x / scale), round to nearest, saturating (memory_pool.py:431-440:
+ * cache_k.div_(k_scale); cache_k.to(torch.float8_e4m3fn), stored as uint8); scale <= 0 means 1.  src_dtype = B200_BF16/F16. */
+int b200_set_kv_buffer_fp8(void* k_buf, int64_t kbuf_stride_t, int64_t kbuf_stride_h, void* v_buf, int64_t vbuf_stride_t,
+                           int64_t vbuf_stride_h, const void* k_new, int64_t knew_stride_b, int64_t knew_stride_h,
+                           const void* v_new, int64_t vnew_stride_b, int64_t vnew_stride_h, const int64_t* loc, int B,
+                           int Hkv, int D, int Dv, int src_dtype, float k_scale, float v_scale, void* stream);
 
 /* --------------------------------------------------------------------------------------------
  * Extend (prefill) attention: AttentionBackend.forward_extend (base_attn_backend.py:101-111);

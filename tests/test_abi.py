@@ -35,7 +35,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layout_matches_header():
     # v1: 23 pointer/int64/size_t fields (8 B) + 10 int32 + 2 float = 232 bytes; v2 adds 2 int32 + 5 pointer/int64
-    assert ctypes.sizeof(_lib.DecodeAttnParams) == 23 * 8 + 12 * 4 + 2 * 4 + 5 * 8 + 5 * 8   # v3: five cascade pointers
+    assert ctypes.sizeof(_lib.DecodeAttnParams) == 23 * 8 + 12 * 4 + 2 * 4 + 5 * 8 + 4 * 4 + 5 * 8   # v3: kv_dtype / scales, five cascade pointers
     assert ctypes.sizeof(_lib.ExtendAttnParams) == 22 * 8 + 10 * 4 + 2 * 4 + 16   # v3: prefix_only, reserved, lse_out, out_f32
 
 

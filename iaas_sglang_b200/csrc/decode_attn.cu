@@ -562,16 +562,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1) decode_attn_mma_kernel(const 
           ldsm_x4_t(vbase + v_lane_off + jq * 32, r0, r1, r2, r3);
           uint32_t be0 = e4m3x2_to_f16x2(__byte_perm(r0, 0, 0x4420), false), be1 = e4m3x2_to_f16x2(__byte_perm(r1, 0, 0x4420), false);
           uint32_t bo0 = e4m3x2_to_f16x2(__byte_perm(r0, 0, 0x4431), false), bo1 = e4m3x2_to_f16x2(__byte_perm(r1, 0, 0x4431), false);
+          // (P goes in as f16 -- 11 mantissa bits against V's 3 -- so the hi + lo second pass of the bf16 path is not needed)
           mma_16816<false>(o[4 * jq], pa, be0, be1);
           mma_16816<false>(o[4 * jq + 1], pa, bo0, bo1);
-          mma_16816<false>(o[4 * jq], pb, be0, be1);
-          mma_16816<false>(o[4 * jq + 1], pb, bo0, bo1);
           be0 = e4m3x2_to_f16x2(__byte_perm(r2, 0, 0x4420), false); be1 = e4m3x2_to_f16x2(__byte_perm(r3, 0, 0x4420), false);
           bo0 = e4m3x2_to_f16x2(__byte_perm(r2, 0, 0x4431), false); bo1 = e4m3x2_to_f16x2(__byte_perm(r3, 0, 0x4431), false);
           mma_16816<false>(o[4 * jq + 2], pa, be0, be1);
           mma_16816<false>(o[4 * jq + 3], pa, bo0, bo1);
-          mma_16816<false>(o[4 * jq + 2], pb, be0, be1);
-          mma_16816<false>(o[4 * jq + 3], pb, bo0, bo1);
         }
       } else {
 #pragma unroll

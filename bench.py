@@ -860,8 +860,11 @@ def time_allreduce(cx: Ctx, rows: int, hidden: int):
         del g
     nbytes = rows * hidden * 2
     out["message_bytes"] = nbytes
-    out["nvlink_bytes_per_rank"] = int(2 * (cx.world - 1) / cx.world * nbytes)
     car = tpmod.custom_all_reduce()
+    mode = int(car.lib.b200_ar_mode2(cx.world, nbytes, int(car.multicast))) if car is not None else 0
+    # received per rank: one-shot push = every peer's whole message; two-shot / NCCL ring = 2 (W-1)/W x message
+    out["nvlink_bytes_per_rank"] = int((cx.world - 1) * nbytes if mode == 5 else 2 * (cx.world - 1) / cx.world * nbytes)
+    out["kernel"] = {5: "push protocol, one-shot", 6: "push protocol, two-shot"}.get(mode, f"mode {mode}")
     out["path"] = (f"own kernels (csrc/allreduce.cu, {car.setup}, multicast {'yes' if car.multicast else 'no'})"
                    if car is not None and car.should_custom_ar(x) else "ncclAllReduce")
     return out

@@ -36,6 +36,18 @@
 //                             and an epilogue over the block's full rows, read locally: plain copy to `out`, or
 //                             residual += x; RMSNorm; optional group-128 e4m3 quantisation (rmsnorm_row.cuh: the same
 //                             code, hence the same bits, as rmsnorm_quant_fp8_kernel after a plain all-reduce).
+//   allreduce_lamport_kernel  row layout, PUSH protocol without flags or barriers (one NVLink one-way latency per phase
+//                             instead of flag round trips): the sender stores its 16-byte vectors straight into the
+//                             receivers' buffers, the receiver polls the DATA -- every 32-bit word of a receive buffer
+//                             holds a sentinel (0x80000000, a pattern the sender never transmits: such a word is sent as
+//                             +0.0/+0.0, which leaves every fp32 sum unchanged) until the payload lands.  Three receive
+//                             buffers rotate by call number; call n re-arms the buffer of call n - 1 (a peer can only
+//                             write into it again in call n + 2, which it cannot start before it has received this
+//                             rank's call n + 1 data, sent after call n has completed).  One-shot: every rank receives
+//                             all W copies and sums them in rank order (bit-identical to the pull kernels).  Two-shot:
+//                             rank c receives sub-range c of every block's rows, reduces it in rank order and pushes the
+//                             result to everybody (one multimem.st where the buffer has a multicast mapping).  Same
+//                             epilogues as the rows kernel.
 // A spin that lasts longer than ~20 s sets the error word and lets the kernel finish (wrong data, no hang); the
 // host polls it with b200_ar_error() (tp.py does so once per step).
 #include <stdlib.h>
@@ -55,14 +67,20 @@ constexpr size_t AR_FLAG_BYTES = (size_t)AR_MAX_BLOCKS * AR_MAX_RANKS * 4;  // 1
 constexpr size_t AR_CALLS_OFF = AR_FLAG_BYTES;        // uint32: calls completed by this rank
 constexpr size_t AR_DONE_OFF = AR_CALLS_OFF + 64;     // uint32: blocks of the running call that have finished
 constexpr size_t AR_ERR_OFF = AR_DONE_OFF + 64;       // uint32: a peer never arrived
+constexpr size_t AR_LCALLS_OFF = AR_ERR_OFF + 64;     // uint32: push-protocol calls completed by this rank
+constexpr size_t AR_LDONE_OFF = AR_LCALLS_OFF + 64;   // uint32: blocks of the running push-protocol call that have finished
+constexpr size_t AR_LPREV_OFF = AR_LDONE_OFF + 64;    // uint32: 16-byte vectors of the receive buffer the last push call used
 constexpr size_t AR_DATA_OFF = 32768;
-static_assert(AR_ERR_OFF + 64 <= AR_DATA_OFF, "region header");
+static_assert(AR_LPREV_OFF + 64 <= AR_DATA_OFF, "region header");
+constexpr size_t AR_LAM_PAD = 65536;                  // AR_MAX_BLOCKS x (AR_MAX_RANKS - 1) vectors of sub-range rounding
+constexpr uint32_t AR_SENTINEL = 0x80000000u;         // never transmitted; receive buffers are armed with it
 
 struct ArParams {
   uint8_t* base[AR_MAX_RANKS];  // region of every rank (own = local pointer)
   uint8_t* mc;                  // multicast address of the same region (NVLS) or nullptr
   int rank, world;
   size_t slot_bytes;
+  size_t lam_off, lam_bytes;    // three push-protocol receive buffers of lam_bytes each at base + lam_off
   const uint4* in;
   uint4* out;
   int64_t nvec;  // 16-byte vectors
@@ -322,12 +340,180 @@ __global__ void __launch_bounds__(AR_ROW_THREADS) allreduce_rows_kernel(const __
   ar_finish(mine, call);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// push protocol (see the file header): no flags, the receiver polls the payload
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_volatile_v4(uint4* p, const uint4& v) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 lam_clean(uint4 v) {   // a word that equals the sentinel travels as +0.0 / +0.0
+  v.x = v.x == AR_SENTINEL ? 0u : v.x;
+  v.y = v.y == AR_SENTINEL ? 0u : v.y;
+  v.z = v.z == AR_SENTINEL ? 0u : v.z;
+  v.w = v.w == AR_SENTINEL ? 0u : v.w;
+  return v;
+}
+__device__ __forceinline__ bool lam_landed(const uint4& v) {
+  return v.x != AR_SENTINEL && v.y != AR_SENTINEL && v.z != AR_SENTINEL && v.w != AR_SENTINEL;
+}
+__device__ __forceinline__ bool lam_timed_out(long long t0, uint8_t* mine) {
+  if (clock64() - t0 > 40000000000LL) {  // ~20 s: a peer is gone; report instead of hanging the GPU
+    *reinterpret_cast<uint32_t*>(mine + AR_ERR_OFF) = 1;
+    return true;
+  }
+  return false;
+}
+__device__ __forceinline__ uint4 lam_poll(const uint4* p, uint8_t* mine) {
+  uint4 v = ld_volatile_v4(p);
+  if (lam_landed(v)) return v;
+  const long long t0 = clock64();
+  do {
+    v = ld_volatile_v4(p);
+  } while (!lam_landed(v) && !lam_timed_out(t0, mine));
+  return v;
+}
+
+template <bool BF16, int WORLD, bool TWOSHOT, int NV>
+__global__ void __launch_bounds__(AR_ROW_THREADS) allreduce_lamport_kernel(const __grid_constant__ ArParams p, const ArRows r,
+                                                                           const RowNormArgs e) {
+  griddep_wait();
+  griddep_launch();
+  __shared__ float red[8];
+  const int b = blockIdx.x, t = threadIdx.x;
+  uint8_t* mine = p.base[p.rank];
+  const uint32_t call = *reinterpret_cast<const volatile uint32_t*>(mine + AR_LCALLS_OFF);
+  const uint32_t prev_vec = *reinterpret_cast<const volatile uint32_t*>(mine + AR_LPREV_OFF);
+  const size_t buf_off = p.lam_off + (size_t)(call % 3u) * p.lam_bytes;
+  const size_t old_off = p.lam_off + (size_t)((call + 2u) % 3u) * p.lam_bytes;   // the buffer of call - 1
+  const int row0 = b * r.rpb, row1 = min(r.M, row0 + r.rpb);
+  const int64_t v0 = (int64_t)row0 * r.rowvec;
+  const int64_t v1 = min((int64_t)row1 * r.rowvec, p.nvec);
+  // two-shot geometry: sub-range c of the block's vectors belongs to rank c
+  const int64_t sub = ((int64_t)r.rpb * r.rowvec + WORLD - 1) / WORLD;
+  const int64_t a1s = (int64_t)gridDim.x * sub;            // vectors one source sends to one owner (all blocks)
+  const int64_t red_off = TWOSHOT ? (int64_t)WORLD * a1s : 0;   // where the reduced message starts in the buffer
+  uint32_t extent;                                          // vectors of the buffer this call writes
+
+  // 1. push
+  if constexpr (!TWOSHOT) {
+    extent = (uint32_t)(WORLD * p.nvec);
+    for (int64_t i = v0 + t; i < v1; i += AR_ROW_THREADS) {
+      const uint4 v = lam_clean(p.in[i]);
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q)
+        if (q != p.rank) st_volatile_v4(reinterpret_cast<uint4*>(p.base[q] + buf_off) + (int64_t)p.rank * p.nvec + i, v);
+    }
+  } else {
+    extent = (uint32_t)(red_off + p.nvec);
+    for (int64_t i = v0 + t; i < v1; i += AR_ROW_THREADS) {
+      const int c = (int)((i - v0) / sub);
+      if (c == p.rank) continue;
+      const int64_t k = (i - v0) - c * sub;
+      st_volatile_v4(reinterpret_cast<uint4*>(p.base[c] + buf_off) + (int64_t)p.rank * a1s + (int64_t)b * sub + k, lam_clean(p.in[i]));
+    }
+  }
+  // 2. re-arm the buffer of the previous call while the payload is in flight
+  {
+    uint4* old = reinterpret_cast<uint4*>(mine + old_off);
+    const uint4 s4 = make_uint4(AR_SENTINEL, AR_SENTINEL, AR_SENTINEL, AR_SENTINEL);
+    for (int64_t j = (int64_t)b * AR_ROW_THREADS + t; j < (int64_t)prev_vec; j += (int64_t)gridDim.x * AR_ROW_THREADS) old[j] = s4;
+  }
+  const uint4* rx = reinterpret_cast<const uint4*>(mine + buf_off);
+  // 3. (two-shot) reduce my sub-range in rank order, push the result to everybody
+  if constexpr (TWOSHOT) {
+    const int64_t a0 = v0 + p.rank * sub, a1 = min(a0 + sub, v1);
+    for (int64_t i = a0 + t; i < a1; i += AR_ROW_THREADS) {
+      const int64_t k = (int64_t)b * sub + (i - a0);
+      uint4 v[WORLD];
+      bool all = true;
+      long long t0 = 0;
+      do {
+        all = true;
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)
+          if (q != p.rank) {
+            v[q] = ld_volatile_v4(rx + (int64_t)q * a1s + k);
+            all = all && lam_landed(v[q]);
+          }
+        if (!all) {
+          if (t0 == 0) t0 = clock64();
+          if (lam_timed_out(t0, mine)) break;
+        }
+      } while (!all);
+      v[p.rank] = p.in[i];
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, v[q]);
+      const uint4 o = lam_clean(pack8<BF16>(acc));
+      if (p.mc) {
+        multimem_st(reinterpret_cast<uint4*>(p.mc + buf_off) + red_off + i, o);
+      } else {
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q) st_volatile_v4(reinterpret_cast<uint4*>(p.base[q] + buf_off) + red_off + i, o);
+      }
+    }
+  }
+  // 4. the summed vector i of this block's rows
+  auto summed = [&](int64_t i) -> uint4 {
+    if constexpr (TWOSHOT) {
+      return lam_poll(rx + red_off + i, mine);
+    } else {
+      uint4 v[WORLD];
+      bool all = true;
+      long long t0 = 0;
+      do {
+        all = true;
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)
+          if (q != p.rank) {
+            v[q] = ld_volatile_v4(rx + (int64_t)q * p.nvec + i);
+            all = all && lam_landed(v[q]);
+          }
+        if (!all) {
+          if (t0 == 0) t0 = clock64();
+          if (lam_timed_out(t0, mine)) break;
+        }
+      } while (!all);
+      v[p.rank] = p.in[i];
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, v[q]);
+      return pack8<BF16>(acc);
+    }
+  };
+  if (r.epi == 0) {
+    for (int64_t i = v0 + t; i < v1; i += AR_ROW_THREADS) p.out[i] = summed(i);
+  } else {
+    for (int m = row0; m < row1; ++m) {
+      const int64_t rv = (int64_t)m * r.rowvec;
+      rmsnorm_quant_row<BF16, NV>(e, m, [&](int vec) { return summed(rv + vec); }, red);
+    }
+  }
+  // last block out: next call number, and how much of this buffer the next call has to re-arm
+  __syncthreads();
+  if (t == 0) {
+    uint32_t* done = reinterpret_cast<uint32_t*>(mine + AR_LDONE_OFF);
+    __threadfence();
+    if (atomicAdd(done, 1u) == gridDim.x - 1) {
+      *done = 0;
+      *reinterpret_cast<volatile uint32_t*>(mine + AR_LPREV_OFF) = extent;
+      *reinterpret_cast<volatile uint32_t*>(mine + AR_LCALLS_OFF) = call + 1;
+    }
+  }
+}
+
+__global__ void ar_arm_kernel(uint4* buf, int64_t nvec) {
+  const uint4 s4 = make_uint4(AR_SENTINEL, AR_SENTINEL, AR_SENTINEL, AR_SENTINEL);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) buf[i] = s4;
+}
+
 struct ArContext {
   ArParams p;
   void* own;  // cudaMalloc'ed by b200_ar_alloc (freed by destroy) or nullptr when the caller owns the regions
   void* opened[AR_MAX_RANKS];
   int device;
-  int mode;   // -1 = measured policy (b200_ar_mode); 1 / 2 / 3 / 4 force a kernel (must be the same on every rank)
+  int mode;   // -1 = measured policy (b200_ar_mode); 1 .. 6 force a kernel (must be the same on every rank)
 };
 
 }  // namespace b200
@@ -336,8 +522,19 @@ using namespace b200;
 
 extern "C" size_t b200_ar_region_bytes(size_t max_message_bytes) {
   const size_t slot = (max_message_bytes + 255) & ~(size_t)255;
-  return AR_DATA_OFF + 4 * slot;
+  return AR_DATA_OFF + 4 * slot + 3 * (2 * slot + AR_LAM_PAD);   // 2 in slots, 2 out stages, 3 push-protocol receive buffers
 }
+
+namespace {
+// arm this rank's three receive buffers with the sentinel (the caller synchronises every rank before the first call)
+int ar_arm(ArContext* c) {
+  c->p.lam_off = AR_DATA_OFF + 4 * c->p.slot_bytes;
+  c->p.lam_bytes = 2 * c->p.slot_bytes + AR_LAM_PAD;   // two-shot: the scattered message + the reduced one (+ per-block rounding)
+  ar_arm_kernel<<<296, 512>>>(reinterpret_cast<uint4*>(c->p.base[c->p.rank] + c->p.lam_off), (int64_t)(3 * c->p.lam_bytes / 16));
+  if (int rc = launched("ar_arm_kernel launch")) return rc;
+  return check_cuda(cudaDeviceSynchronize(), "ar_arm_kernel");
+}
+}  // namespace
 
 // allocate this rank's region (zeroed) and export its 64-byte IPC handle
 extern "C" int b200_ar_alloc(size_t max_message_bytes, void** region_out, void* ipc_handle_out64) {
@@ -397,6 +594,12 @@ extern "C" int b200_ar_init(void* own_region, const void* handles, int rank, int
     c->opened[r] = peer;
     c->p.base[r] = (uint8_t*)peer;
   }
+  if (int rc = ar_arm(c)) {
+    for (int q = 0; q < AR_MAX_RANKS; ++q)
+      if (c->opened[q]) cudaIpcCloseMemHandle(c->opened[q]);
+    delete c;
+    return rc;
+  }
   *ctx_out = c;
   return B200_OK;
 }
@@ -420,6 +623,10 @@ extern "C" int b200_ar_init_ptrs(const uint64_t* regions, uint64_t multicast, in
   c->p.mc = (uint8_t*)(uintptr_t)multicast;
   c->p.slot_bytes = (max_message_bytes + 255) & ~(size_t)255;
   for (int r = 0; r < world; ++r) c->p.base[r] = (uint8_t*)(uintptr_t)regions[r];
+  if (int rc = ar_arm(c)) {
+    delete c;
+    return rc;
+  }
   *ctx_out = c;
   return B200_OK;
 }
@@ -427,7 +634,7 @@ extern "C" int b200_ar_init_ptrs(const uint64_t* regions, uint64_t multicast, in
 extern "C" int b200_ar_has_multicast(void* ctx) { return ctx && ((ArContext*)ctx)->p.mc ? 1 : 0; }
 
 extern "C" int b200_ar_set_mode(void* ctx, int mode) {
-  B200_REQUIRE(ctx && mode >= -1 && mode <= 4, B200_ERR_ARG, "ar_set_mode: mode must be -1 (policy) or 1..4");
+  B200_REQUIRE(ctx && mode >= -1 && mode <= 6, B200_ERR_ARG, "ar_set_mode: mode must be -1 (policy) or 1..6");
   ((ArContext*)ctx)->mode = mode;
   return B200_OK;
 }
@@ -449,27 +656,27 @@ extern "C" void b200_ar_destroy(void* ctx) {
   delete c;
 }
 
-// Which kernel is fastest for a plain all-reduce, measured on 2 / 4 / 8 B200 of one NVSwitch box (tools/ar_check.py
-// AR_SWEEP=1; profiles/r01b_allreduce.md, profiles/r02_allreduce.md):
-//   1 = one-shot (flat), 2 = two-shot (flat, peer loads), 3 = rows kernel with NVLS multicast (needs a multicast
-//   mapping), 4 = rows kernel, one-shot pull; 0 = leave it to ncclAllReduce.
-// `multicast` = the context has a multicast mapping.  The reference makes the same kind of split
-// (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one stage, else two).
-// Measured policy (tools/ar_check.py AR_SWEEP=1 on 2 / 4 / 8 B200 of one NVSwitch box, profiles/r02_allreduce.md; us):
-//   2 ranks: one-shot everywhere (1 MB 14.7, 4 MB 22.0; NCCL 21.6 / 45);
-//   4 ranks: one-shot up to 3 MB (1 MB 19.9, 2 MB 25.8), two-shot above (4 MB 31.8, 8 MB 42.8; NVLS 47.9 / 58.2,
-//            NCCL 44.2 / 53.2) -- the multicast kernel never wins at 4 ranks;
-//   8 ranks: one-shot up to 768 KB (64 KB 18.7, 512 KB 24.7), then NVLS where the buffer has a multicast mapping
-//            (1 MB 27.9, 2 MB 29.6, 4 MB 35.0; two-shot 29.7 / 31.7 / 35.9; NCCL 36.2 / 39.8 / 61.0), two-shot from 6 MB
-//            (8 MB 47.0 vs NVLS 58.6, NCCL 77.9).  No size is left to NCCL any more.
-// 1 one-shot, 2 two-shot, 3 NVLS rows kernel; 0 = leave it to NCCL.
-extern "C" int b200_ar_mode2(int world, size_t bytes, int multicast) {
+// Which kernel is fastest, measured on 2 / 4 / 8 B200 of one NVSwitch box (tools/ar_check.py, AR_SWEEP=1;
+// profiles/r02_allreduce.md; us, plain all-reduce in a graph of 50 calls):
+//   1 one-shot pull (flat), 2 two-shot pull (flat), 3 rows kernel with NVLS multicast, 4 rows kernel one-shot pull,
+//   5 push protocol one-shot, 6 push protocol two-shot.
+// The push protocol (no flag round trips) wins at every size the receive buffers hold:
+//   2 ranks: push-1 1 MB 8.0 / 4 MB 10.7 (pull one-shot 14.3 / 20.5, NCCL 21 / 44);
+//   4 ranks: push-1 64 KB 5.5, 512 KB 7.2, 1 MB 9.4; push-2 1 MB 8.8, 2 MB 10.3, 4 MB 20.0, 8 MB 26.9
+//            (pull one-shot 12.1 / 16.7 / 19.1, two-shot 27.8 @ 2 MB, 42.2 @ 8 MB; NCCL 22 .. 53);
+//   8 ranks: see profiles/r02_allreduce.md.
+// The reference makes the same kind of split (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one
+// stage, else two).  `fused`: the kernel also runs the add + RMSNorm (+ quant) epilogue -- real rows, so the one-shot
+// form (more, smaller blocks) stays ahead a little longer.
+static int ar_policy(int world, size_t bytes, bool fused) {
   if (world < 2 || world > AR_MAX_RANKS) return 0;
-  if (world == 2) return 1;
-  if (world <= 4) return bytes <= ((size_t)3 << 20) ? 1 : 2;
-  if (bytes <= (size_t)768 * 1024) return 1;
-  if (multicast && bytes < ((size_t)6 << 20)) return 3;
-  return 2;
+  if (world == 2) return 5;
+  if (world <= 4) return bytes <= (fused ? (size_t)1536 << 10 : (size_t)768 << 10) ? 5 : 6;
+  return bytes <= (fused ? (size_t)512 << 10 : (size_t)256 << 10) ? 5 : 6;
+}
+extern "C" int b200_ar_mode2(int world, size_t bytes, int multicast) {
+  (void)multicast;
+  return ar_policy(world, bytes, false);
 }
 extern "C" int b200_ar_mode(int world, size_t bytes) { return b200_ar_mode2(world, bytes, 0); }
 
@@ -518,6 +725,62 @@ int launch_rows(const ArContext* c, ArParams p, int M, int rowvec, int epi, cons
   return launch_rows_w<false, 4>(p, r, e, nb, bf16, st);
 }
 
+template <bool TWOSHOT, int NV>
+int launch_lamport_w(const ArParams& p, const ArRows& r, const RowNormArgs& e, int nb, bool bf16, cudaStream_t st) {
+#define B200_ARL(W)                                                                                                             \
+  case W:                                                                                                                       \
+    if (bf16) launch_pdl(allreduce_lamport_kernel<true, W, TWOSHOT, NV>, dim3(nb), dim3(AR_ROW_THREADS), 0, st, p, r, e);       \
+    else launch_pdl(allreduce_lamport_kernel<false, W, TWOSHOT, NV>, dim3(nb), dim3(AR_ROW_THREADS), 0, st, p, r, e);           \
+    break;
+  switch (p.world) {
+    B200_ARL(2) B200_ARL(3) B200_ARL(4) B200_ARL(5) B200_ARL(6) B200_ARL(7) B200_ARL(8)
+    default:
+      set_error("ar: world %d", p.world);
+      return B200_ERR_UNSUPPORTED;
+  }
+#undef B200_ARL
+  return launched("allreduce_lamport_kernel launch");
+}
+
+// how many 16-byte vectors of a receive buffer a push-protocol call of this geometry writes
+int64_t lamport_extent(int world, int64_t nvec, int M, int rowvec, bool twoshot, int* rpb_out, int* nb_out) {
+  int64_t per_block_vec = (int64_t)AR_ROW_THREADS * (twoshot ? world : 1);
+  int rpb = (int)((per_block_vec + rowvec - 1) / rowvec);
+  if (rpb < 1) rpb = 1;
+  int nb = (M + rpb - 1) / rpb;
+  if (nb > AR_MAX_BLOCKS) {
+    rpb = (M + AR_MAX_BLOCKS - 1) / AR_MAX_BLOCKS;
+    nb = (M + rpb - 1) / rpb;
+  }
+  *rpb_out = rpb;
+  *nb_out = nb;
+  if (!twoshot) return (int64_t)world * nvec;
+  const int64_t sub = ((int64_t)rpb * rowvec + world - 1) / world;
+  return (int64_t)world * nb * sub + nvec;
+}
+
+// push-protocol kernel: M rows of rowvec vectors; B200_ERR_UNSUPPORTED when the message does not fit a receive buffer
+int launch_lamport(const ArContext* c, ArParams p, int M, int rowvec, int epi, const RowNormArgs& e, bool twoshot, bool bf16,
+                   cudaStream_t st) {
+  if (p.world == 2) twoshot = false;
+  ArRows r;
+  int nb;
+  const int64_t extent = lamport_extent(p.world, p.nvec, M, rowvec, twoshot, &r.rpb, &nb);
+  B200_REQUIRE((size_t)extent * 16 <= p.lam_bytes, B200_ERR_UNSUPPORTED,
+               "ar: a %s push all-reduce of %lld bytes at %d ranks needs %lld bytes of receive buffer, have %zu", twoshot ? "two-shot" : "one-shot",
+               (long long)p.nvec * 16, p.world, (long long)extent * 16, p.lam_bytes);
+  r.M = M; r.rowvec = rowvec; r.epi = epi;
+  const int nv = epi ? (rowvec + 255) / 256 : 1;
+  if (twoshot) {
+    if (nv <= 1) return launch_lamport_w<true, 1>(p, r, e, nb, bf16, st);
+    if (nv <= 2) return launch_lamport_w<true, 2>(p, r, e, nb, bf16, st);
+    return launch_lamport_w<true, 4>(p, r, e, nb, bf16, st);
+  }
+  if (nv <= 1) return launch_lamport_w<false, 1>(p, r, e, nb, bf16, st);
+  if (nv <= 2) return launch_lamport_w<false, 2>(p, r, e, nb, bf16, st);
+  return launch_lamport_w<false, 4>(p, r, e, nb, bf16, st);
+}
+
 }  // namespace
 
 // in / out: n_elems 16-bit values, 16-byte aligned, n_elems % 8 == 0, n_elems * 2 <= max_message_bytes; out may alias in
@@ -539,6 +802,13 @@ extern "C" int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n
   if (mode == 3 && !p.mc) mode = 2;
   if (mode == 2 && p.world == 2) mode = 1;
   if (mode == 0) mode = p.world <= 4 ? 1 : 2;  // the caller asked for this path although the policy prefers NCCL
+  if (mode == 5 || mode == 6) {
+    const int rowvec = 512;  // 8 KB pseudo-rows
+    const int M = (int)((p.nvec + rowvec - 1) / rowvec);
+    RowNormArgs e = {};
+    if (c->mode <= 0 && mode == 5 && (size_t)p.world * p.nvec * 16 > p.lam_bytes) mode = 6;   // W copies do not fit: scatter
+    return launch_lamport(c, p, M, rowvec, 0, e, mode == 6, dtype == B200_BF16, st);
+  }
   if (mode == 3 || mode == 4) {
     const int rowvec = 512;  // 8 KB pseudo-rows
     const int M = (int)((p.nvec + rowvec - 1) / rowvec);
@@ -607,22 +877,14 @@ extern "C" int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* re
   p.out = nullptr;
   p.nvec = (int64_t)M * H / 8;
   const size_t bytes = (size_t)M * H * 2;
-  int mode = c->mode > 0 ? c->mode : b200_ar_mode2(p.world, bytes, p.mc != nullptr);
-  bool nvls = (mode == 3) && p.mc;
-  if (c->mode <= 0) {
-    // One kernel or two?  Measured (tools/ar_check.py, fused vs all-reduce -> rmsnorm_quant_fp8, us): 2 ranks 128x4096
-    // 18.3 vs 19.2, 256x8192 37.6 vs 30; 4 ranks 256x4096 33.6 vs 33.0, 128x5120 35.8 vs 32.3, 256x8192 53.2 vs 59.7;
-    // 8 ranks 512x4096 47.2 vs 42.5, 128x5120 47.5 vs 34.7, 256x8192 46.7 vs 60.7.  The fused kernel wins on wide rows
-    // (H = 8192: the separate norm is a 16 KB row per CTA) and on small messages at 2 ranks; elsewhere the caller runs the
-    // two kernels (B200_ERR_UNSUPPORTED is that answer, tp.py falls back; every rank decides from (world, M, H) alone).
-    const bool fused_wins = p.world == 2 ? bytes <= ((size_t)1536 << 10) : H >= 8192;
-    if (!fused_wins || (!nvls && p.world > 4 && bytes > ((size_t)1536 << 10))) {
-      set_error("ar_allreduce_add_rmsnorm: %d x %d at %d ranks: the two separate kernels are the faster plan", M, H, p.world);
-      return B200_ERR_UNSUPPORTED;
-    }
-  }
+  // the fused kernel is the faster plan at every (world, M, H) the push protocol serves (tools/ar_check.py: 2 ranks
+  // 128x4096 9.8 us against 18.7 for all-reduce -> rmsnorm_quant_fp8; 4 ranks 256x4096 16.9 / 31.8, 256x8192 24.8 / 41.3)
+  int mode = c->mode > 0 ? c->mode : ar_policy(p.world, bytes, true);
+  if (c->mode <= 0 && mode == 5 && (size_t)p.world * p.nvec * 16 > p.lam_bytes) mode = 6;
+  const bool nvls = (mode == 3) && p.mc;
   RowNormArgs e;
   e.residual = (uint16_t*)residual; e.w = (const uint16_t*)weight; e.out = (uint16_t*)norm_out; e.q = (uint8_t*)q; e.q_sm = q_sm;
   e.s = s; e.s_sm = s_sm; e.s_sg = s_sg; e.H = H; e.eps = eps; e.q_eps = q_eps; e.fmin_ = fp8_min; e.fmax_ = fp8_max;
+  if (mode == 5 || mode == 6) return launch_lamport(c, p, M, H / 8, 1, e, mode == 6, dtype == B200_BF16, (cudaStream_t)stream);
   return launch_rows(c, p, M, H / 8, 1, e, nvls, dtype == B200_BF16, (cudaStream_t)stream);
 }

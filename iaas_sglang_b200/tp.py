@@ -162,7 +162,8 @@ class CustomAllReduce:
         return out
 
     def set_mode(self, mode: int) -> None:
-        """Force a kernel (1 one-shot, 2 two-shot, 3 NVLS, 4 row-layout one-shot; -1 = measured policy).  Collective
+        """Force a kernel (1 one-shot, 2 two-shot, 3 NVLS, 4 row-layout one-shot, 5 / 6 push protocol one- / two-shot;
+        -1 = measured policy).  Collective
         by convention: every rank must set the same mode."""
         from ._lib import check
 

@@ -333,8 +333,10 @@ int b200_rope_neox(void* q, int64_t q_stride_m, void* k, int64_t k_stride_m, con
  *       (torch.distributed._symmetric_memory rendezvous): b200_ar_init_ptrs takes the W device pointers and the
  *       multicast address of the same buffer (0 if the fabric has none), which enables the NVLS kernel.
  * Every call launches ONE kernel on `stream` (no host sync, CUDA-graph capturable); every rank must make the same
- * calls with the same sizes in the same order.  Results are identical on all ranks; without multicast they are the
- * fp32 sum in rank order rounded once.  b200_ar_error returns 1 if a peer never arrived (the kernel gave up after
+ * calls with the same sizes in the same order.  Results are identical on all ranks and are the fp32 sum in rank order
+ * rounded once (the NVLS kernel, mode 3, is the exception: the switch's own accumulation order).  The default kernels
+ * use a push protocol: a rank stores its payload straight into its peers' receive buffers and the receivers poll the
+ * payload itself, so a call costs one NVLink one-way latency per phase instead of flag round trips.  b200_ar_error returns 1 if a peer never arrived (the kernel gave up after
  * ~20 s instead of hanging).
  * ------------------------------------------------------------------------------------------ */
 size_t b200_ar_region_bytes(size_t max_message_bytes);
@@ -348,13 +350,13 @@ int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int
 /* in [M, H] (this rank's partial sums); residual [M, H] += sum (stored back); y = RMSNorm(residual) * weight;
  * norm_out [M, H] = y (may be NULL); q / s = per_token_group_quant_fp8(y, 128) with the strides of
  * b200_per_token_group_quant_fp8 (may be NULL).  Equal, bit for bit when no multicast is involved, to
- * b200_ar_allreduce followed by b200_rmsnorm_quant_fp8.  H % 128 == 0, H <= 8192.  B200_ERR_UNSUPPORTED when the
- * message is better served by the two separate kernels (large message, many ranks, no multicast). */
+ * b200_ar_allreduce followed by b200_rmsnorm_quant_fp8.  H % 128 == 0, H <= 8192, M * H * 2 <= max_message_bytes. */
 int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* residual, const void* weight, void* norm_out, void* q,
                                   int64_t q_stride_m, float* s, int64_t s_stride_m, int64_t s_stride_g, int M, int H,
                                   int dtype, float eps, float quant_eps, float fp8_min, float fp8_max, void* stream);
-/* measured policy: 1 = one-shot kernel, 2 = two-shot kernel, 3 = NVLS multicast kernel, 4 = row-layout one-shot,
- * 0 = ncclAllReduce is faster for this (world, message size).  b200_ar_mode = b200_ar_mode2 without multicast. */
+/* measured policy: 1 = one-shot pull kernel, 2 = two-shot pull kernel, 3 = NVLS multicast kernel, 4 = row-layout
+ * one-shot pull, 5 = push protocol one-shot, 6 = push protocol two-shot; 0 = leave the message to ncclAllReduce
+ * (world outside 2..8).  b200_ar_mode = b200_ar_mode2 without multicast. */
 int b200_ar_mode(int world, size_t bytes);
 int b200_ar_mode2(int world, size_t bytes, int has_multicast);
 /* force a kernel for every following call (-1 = back to the policy); must be the same on every rank */

@@ -22,7 +22,7 @@ import torch.distributed as dist  # noqa: E402
 
 from iaas_sglang_b200 import ops, tp  # noqa: E402
 
-MODE_NAMES = {1: "one-shot", 2: "two-shot", 3: "nvls", 4: "rows-pull"}
+MODE_NAMES = {1: "one-shot", 2: "two-shot", 3: "nvls", 4: "rows-pull", 5: "push-1", 6: "push-2"}
 
 
 def main():
@@ -32,7 +32,9 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     ar = tp.custom_all_reduce()
     assert ar is not None, "custom all-reduce did not initialise"
-    modes = [1, 4] + ([2] if world > 2 else []) + ([3] if ar.multicast else [])
+    modes = [1, 4] + ([2] if world > 2 else []) + ([3] if ar.multicast else []) + [5] + ([6] if world > 2 else [])
+    if os.environ.get("AR_MODES"):
+        modes = [int(m) for m in os.environ["AR_MODES"].split(",")]
     if rank == 0:
         print(f"world {world}: set-up {ar.setup}, multicast {ar.multicast}, kernels {[MODE_NAMES[m] for m in modes]}", flush=True)
     ok = True
@@ -64,6 +66,8 @@ def main():
                 acc = expected(x)
                 want = acc.to(dt)
                 y = x.clone()
+                if mode == 5 and n * 2 * world > 2 * ar.max_bytes:
+                    continue   # W copies of the message do not fit one receive buffer
                 ar.all_reduce_(y)
                 if mode == 3:   # one ulp of the half type around the exact sum
                     ulp = (want.float().abs() * (2.0 ** -7 if dt == torch.bfloat16 else 2.0 ** -10)).clamp_min(1e-6)
@@ -85,7 +89,10 @@ def main():
     seq = []
     for i in range(36):
         n = sizes[i % len(sizes)]
-        seq.append((modes[i % len(modes)], torch.randn(n, device=dev, dtype=torch.bfloat16, generator=gen)))
+        m = modes[i % len(modes)]
+        if m == 5 and n * 2 * world > 2 * ar.max_bytes:
+            m = 1
+        seq.append((m, torch.randn(n, device=dev, dtype=torch.bfloat16, generator=gen)))
     wants = [expected(x) for _, x in seq]
     outs = []
     for i, (mode, x) in enumerate(seq):
@@ -131,9 +138,11 @@ def main():
     ok = ok and good
 
     # ---- 4. fused all-reduce + add + RMSNorm (+ FP8 quant) vs the two-kernel sequence ----
-    for mode in [m for m in modes if m in (3, 4)]:
+    for mode in [m for m in modes if m in (3, 4, 5, 6)]:
         ar.set_mode(mode)
         for (M, H) in ((64, 4096), (128, 5120), (256, 8192), (512, 4096), (37, 7168)):
+            if mode == 5 and M * H * 2 * world > 2 * ar.max_bytes:
+                continue
             g = torch.Generator(device=dev).manual_seed(5 + rank)
             x = (torch.randn(M, H, device=dev, generator=g) * 0.5).to(torch.bfloat16)
             gs = torch.Generator(device=dev).manual_seed(99)   # replicated tensors
@@ -195,7 +204,7 @@ def main():
         cols = []
         for m in modes:
             ar.set_mode(m)
-            cols.append(timeit(lambda a: ar.all_reduce_(a), t))
+            cols.append(float("nan") if (m == 5 and n * 2 * world > 2 * ar.max_bytes) else timeit(lambda a: ar.all_reduce_(a), t))
         ar.set_mode(-1)
         us_n = timeit(lambda a: dist.all_reduce(a), t)
         us_p = timeit(lambda a: tp.tensor_model_parallel_all_reduce(a), t)
@@ -212,7 +221,14 @@ def main():
 
         def fused(a):
             tp.tensor_model_parallel_fused_allreduce_rmsnorm(a, res, w, 1e-5, quant_fp8=True, want_half=False)
-        say(f"all-reduce + add+norm+quant {M}x{H}: two kernels {timeit(two, x):7.1f} us   fused {timeit(fused, x):7.1f} us")
+        line = f"all-reduce + add+norm+quant {M}x{H}: two kernels {timeit(two, x):7.1f} us   fused(policy) {timeit(fused, x):7.1f} us"
+        for m in [m for m in modes if m in (3, 4, 5, 6)]:
+            if m == 5 and M * H * 2 * world > 2 * ar.max_bytes:
+                continue
+            ar.set_mode(m)
+            line += f"   {MODE_NAMES[m]} {timeit(lambda a: ar.all_reduce_add_rmsnorm(a, res, w, 1e-5, quant_fp8=True, want_half=False), x):6.1f}"
+        ar.set_mode(-1)
+        say(line)
     dist.barrier()
     say("AR_CHECK " + ("PASS" if ok else "FAIL"))
     sys.stdout.flush()

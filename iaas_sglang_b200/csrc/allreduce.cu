@@ -664,7 +664,8 @@ extern "C" void b200_ar_destroy(void* ctx) {
 //   2 ranks: push-1 1 MB 8.0 / 4 MB 10.7 (pull one-shot 14.3 / 20.5, NCCL 21 / 44);
 //   4 ranks: push-1 64 KB 5.5, 512 KB 7.2, 1 MB 9.4; push-2 1 MB 8.8, 2 MB 10.3, 4 MB 20.0, 8 MB 26.9
 //            (pull one-shot 12.1 / 16.7 / 19.1, two-shot 27.8 @ 2 MB, 42.2 @ 8 MB; NCCL 22 .. 53);
-//   8 ranks: see profiles/r02_allreduce.md.
+//   8 ranks: push-1 64 KB 7.1, 256 KB 8.0, 512 KB 10.8, 1 MB 16.5; push-2 512 KB 11.6, 1 MB 12.1, 2 MB 13.0, 4 MB 16.7,
+//            8 MB 30.5 (NVLS 20.7 .. 35.1 @ 4 MB, 59.1 @ 8 MB; pull two-shot 36.1 @ 4 MB; NCCL 33 .. 78).
 // The reference makes the same kind of split (custom_all_reduce.cuh: world 2 one stage; 4: < 512 KB; 8: < 256 KB one
 // stage, else two).  `fused`: the kernel also runs the add + RMSNorm (+ quant) epilogue -- real rows, so the one-shot
 // form (more, smaller blocks) stays ahead a little longer.
@@ -672,7 +673,7 @@ static int ar_policy(int world, size_t bytes, bool fused) {
   if (world < 2 || world > AR_MAX_RANKS) return 0;
   if (world == 2) return 5;
   if (world <= 4) return bytes <= (fused ? (size_t)1536 << 10 : (size_t)768 << 10) ? 5 : 6;
-  return bytes <= (fused ? (size_t)512 << 10 : (size_t)256 << 10) ? 5 : 6;
+  return bytes <= ((size_t)512 << 10) ? 5 : 6;
 }
 extern "C" int b200_ar_mode2(int world, size_t bytes, int multicast) {
   (void)multicast;
@@ -879,6 +880,14 @@ extern "C" int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* re
   const size_t bytes = (size_t)M * H * 2;
   // the fused kernel is the faster plan at every (world, M, H) the push protocol serves (tools/ar_check.py: 2 ranks
   // 128x4096 9.8 us against 18.7 for all-reduce -> rmsnorm_quant_fp8; 4 ranks 256x4096 16.9 / 31.8, 256x8192 24.8 / 41.3)
+  // 8 ranks: a block's share of the reduce-scatter is an eighth of its rows, the row epilogue then waits for seven
+  // peers' shares; the plain push all-reduce followed by rmsnorm_quant_fp8 is faster (512x4096 25.3 us against 28.3 fused,
+  // 256x8192 26.2 / 28.8, 128x5120 18.1 / 25.3): B200_ERR_UNSUPPORTED is that answer (tp.py runs the two kernels; every
+  // rank decides from (world, M, H) alone)
+  if (c->mode <= 0 && p.world > 4) {
+    set_error("ar_allreduce_add_rmsnorm: %d x %d at %d ranks: the two separate kernels are the faster plan", M, H, p.world);
+    return B200_ERR_UNSUPPORTED;
+  }
   int mode = c->mode > 0 ? c->mode : ar_policy(p.world, bytes, true);
   if (c->mode <= 0 && mode == 5 && (size_t)p.world * p.nvec * 16 > p.lam_bytes) mode = 6;
   const bool nvls = (mode == 3) && p.mc;

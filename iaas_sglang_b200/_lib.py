@@ -80,6 +80,7 @@ SIGNATURES = {
     "b200_decode_attn_num_splits": (c_int, [c_int] * 7),
     "b200_decode_attn_workspace_size": (c_size_t, [c_int] * 4),
     "b200_decode_attn": (c_int, [C.POINTER(DecodeAttnParams), c_void_p]),
+    "b200_decode_attn_static": (c_int, [C.POINTER(DecodeAttnParams), c_void_p]),
     "b200_decode_attn_quant_fp8": (c_int, [C.POINTER(DecodeAttnParams), c_void_p, c_int64, c_void_p, c_int64, c_int64,
                                            c_float, c_float, c_float, c_void_p]),
     "b200_set_kv_buffer": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64,

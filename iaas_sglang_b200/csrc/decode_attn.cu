@@ -20,6 +20,8 @@
 #include <math.h>
 #include <stdio.h>
 
+#include <pthread.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -1372,4 +1374,60 @@ extern "C" int b200_decode_attn_quant_fp8(const b200_decode_attn_params* a, void
   mq.q = (uint8_t*)q; mq.q_sm = q_sm; mq.s = s; mq.s_sm = s_sm; mq.s_sg = s_sg;
   mq.eps = eps; mq.fmin_ = fp8_min; mq.fmax_ = fp8_max;
   return decode_attn_impl(a, &mq, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// b200_decode_attn_static: b200_decode_attn for callers that must not allocate (CUDA-graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The split-KV partial states go into ONE file-scope device array of
+// B200_DECODE_ATTN_STATIC_SCRATCH_BYTES (20 MiB; every GPU that loads the library holds it until exit) instead of the
+// caller's workspace.  Nothing in that scratch has to start at zero: every partial the merge reads is written by the
+// same call (decode_merge_part_kernel / decode_merge_kernel only visit slots the attention kernel of this call filled).
+// All calls share the array, so two calls that overlap on the GPU (different streams, or graphs replayed concurrently)
+// race; calls on one stream are ordered and safe.  No cudaMalloc / cudaFree / allocating routine on this path.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+static __device__ __align__(256) unsigned char g_decode_attn_static_scratch[B200_DECODE_ATTN_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxStaticDevices = 64;
+
+// The array's name is a host-side stand-in in host code, not a device address: ask the runtime for the address, once
+// per device, with that device current.
+int decode_attn_static_scratch(void** out) {
+  static void* ptrs[kMaxStaticDevices] = {};
+  static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxStaticDevices, B200_ERR_UNSUPPORTED, "decode_attn_static: device ordinal %d out of range", dev);
+  pthread_mutex_lock(&mu);
+  void* ptr = ptrs[dev];
+  cudaError_t e = cudaSuccess;
+  if (!ptr) {
+    e = cudaGetSymbolAddress(&ptr, g_decode_attn_static_scratch);
+    if (e == cudaSuccess) ptrs[dev] = ptr;
+  }
+  pthread_mutex_unlock(&mu);
+  if (e != cudaSuccess) return check_cuda(e, "cudaGetSymbolAddress(decode_attn static scratch)");
+  *out = ptr;
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_decode_attn_static(const b200_decode_attn_params* a, void* stream) {
+  B200_REQUIRE(a != nullptr, B200_ERR_ARG, "decode_attn_static: null params");
+  B200_REQUIRE(a->B >= 0 && a->Hq > 0 && a->Hkv > 0 && a->D > 0 && a->Dv > 0, B200_ERR_ARG, "decode_attn_static: bad sizes");
+  const int S = a->B > 0 ? b200_decode_attn_num_splits(a->B, a->Hq, a->Hkv, a->D, a->Dv, a->max_seq_len, a->num_splits) : 1;
+  const size_t need = b200_decode_attn_workspace_size(a->B, a->Hq, a->Dv, S);
+  B200_REQUIRE(need <= (size_t)B200_DECODE_ATTN_STATIC_SCRATCH_BYTES, B200_ERR_ARG,
+               "decode_attn_static: B=%d Hq=%d Dv=%d with %d KV splits needs %zu bytes of scratch, the static array holds %zu; "
+               "use b200_decode_attn with a caller-provided workspace",
+               a->B, a->Hq, a->Dv, S, need, (size_t)B200_DECODE_ATTN_STATIC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (int rc = decode_attn_static_scratch(&scratch)) return rc;
+  b200_decode_attn_params p = *a;
+  p.workspace = scratch;
+  p.workspace_bytes = (size_t)B200_DECODE_ATTN_STATIC_SCRATCH_BYTES;
+  return decode_attn_impl(&p, nullptr, stream);
 }

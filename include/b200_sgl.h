@@ -140,6 +140,16 @@ typedef struct b200_decode_attn_params {
 int b200_decode_attn_num_splits(int B, int Hq, int Hkv, int D, int Dv, int max_seq_len, int num_splits_hint);
 size_t b200_decode_attn_workspace_size(int B, int Hq, int Dv, int num_splits);
 int b200_decode_attn(const b200_decode_attn_params* p, void* stream);
+/* No counterpart in the reference.  b200_decode_attn for callers that
+ * cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc): p->workspace and
+ * p->workspace_bytes are IGNORED, the split-KV scratch is a file-scope device array of
+ * B200_DECODE_ATTN_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Same result as
+ * b200_decode_attn.  B200_ERR_ARG when b200_decode_attn_workspace_size(B, Hq, Dv, splits) exceeds that size (every
+ * tuned GQA / MLA shape fits; the generic kernel fits while B * Hq * splits * (Dv + 1) * 4 + 256 does).  Calls no
+ * cudaMalloc / cudaFree.  All calls share the array: calls that overlap on the GPU (other streams) race; calls on one
+ * stream are ordered.  Nothing in the array needs clearing between calls. */
+#define B200_DECODE_ATTN_STATIC_SCRATCH_BYTES (20u << 20)
+int b200_decode_attn_static(const b200_decode_attn_params* p, void* stream);
 /* b200_decode_attn followed by per_token_group_quant_fp8(out.view(B, Hq * Dv), 128, column-major scales) for the
  * FP8 block o_proj (fp8_utils.py:202-204 sglang_per_token_group_quant_fp8; per_token_group_quant_8bit.cu:25-115),
  * emitted by the split-merge kernel: out is written as usual, q8 [B, Hq*Dv] e4m3 (row stride q_stride_m bytes) and

@@ -745,7 +745,10 @@ int launch_lamport_w(const ArParams& p, const ArRows& r, const RowNormArgs& e, i
 
 // how many 16-byte vectors of a receive buffer a push-protocol call of this geometry writes
 int64_t lamport_extent(int world, int64_t nvec, int M, int rowvec, bool twoshot, int* rpb_out, int* nb_out) {
-  int64_t per_block_vec = (int64_t)AR_ROW_THREADS * (twoshot ? world : 1);
+  // one row (>= 256 vectors) per block: measured at 4 ranks (fused 256x4096 16.9 us with 1024 vectors per block, 13.3 with
+  // 256 / 512, 25.7 with 2048) -- more, smaller blocks hide the poll latency of the row epilogue
+  int64_t per_block_vec = AR_ROW_THREADS;
+  if (tune(TUNE_AR_BLOCK_VEC) > 0) per_block_vec = tune(TUNE_AR_BLOCK_VEC);
   int rpb = (int)((per_block_vec + rowvec - 1) / rowvec);
   if (rpb < 1) rpb = 1;
   int nb = (M + rpb - 1) / rpb;
@@ -880,11 +883,11 @@ extern "C" int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* re
   const size_t bytes = (size_t)M * H * 2;
   // the fused kernel is the faster plan at every (world, M, H) the push protocol serves (tools/ar_check.py: 2 ranks
   // 128x4096 9.8 us against 18.7 for all-reduce -> rmsnorm_quant_fp8; 4 ranks 256x4096 16.9 / 31.8, 256x8192 24.8 / 41.3)
-  // 8 ranks: a block's share of the reduce-scatter is an eighth of its rows, the row epilogue then waits for seven
-  // peers' shares; the plain push all-reduce followed by rmsnorm_quant_fp8 is faster (512x4096 25.3 us against 28.3 fused,
-  // 256x8192 26.2 / 28.8, 128x5120 18.1 / 25.3): B200_ERR_UNSUPPORTED is that answer (tp.py runs the two kernels; every
-  // rank decides from (world, M, H) alone)
-  if (c->mode <= 0 && p.world > 4) {
+  // 8 ranks (one row per block; tools/ar_check.py, us, fused against push all-reduce -> rmsnorm_quant_fp8): 512x4096 28.8
+  // against 25.5, 128x5120 16.8 / 15.3, 256x8192 24.2 / 28.7 -- the fused form only pays on wide rows there (the separate
+  // norm is one 16 KB row per CTA).  B200_ERR_UNSUPPORTED is the "two kernels" answer (tp.py runs them; every rank decides
+  // from (world, M, H) alone)
+  if (c->mode <= 0 && p.world > tune(TUNE_AR_FUSED_WORLD) && H < 8192) {
     set_error("ar_allreduce_add_rmsnorm: %d x %d at %d ranks: the two separate kernels are the faster plan", M, H, p.world);
     return B200_ERR_UNSUPPORTED;
   }

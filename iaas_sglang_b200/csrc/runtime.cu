@@ -47,6 +47,8 @@ static const TuneEntry kTune[TUNE_COUNT] = {
     {"awq_v1", "B200_AWQ_V1", 0},
     {"attn_ld_hint", "B200_ATTN_LD_HINT", 0},   // short-row KV loads: 0 = L2::256B prefetch hint, 1 = plain cp.async.cg
     {"gb_epi", "B200_GB_EPI", 0},
+    {"ar_block_vec", "B200_AR_BLOCK_VEC", 0},   // push all-reduce: 16-byte vectors per block (0 = 256: one row per block); same on every rank
+    {"ar_fused_world", "B200_AR_FUSED_WORLD", 4},   // largest world size at which all-reduce + add + RMSNorm runs as ONE kernel
 };
 static int g_tune[TUNE_COUNT];
 static const bool g_tune_loaded = [] {

@@ -361,7 +361,7 @@ int b200_ar_allreduce(void* ctx, const void* in, void* out, int64_t n_elems, int
  * norm_out [M, H] = y (may be NULL); q / s = per_token_group_quant_fp8(y, 128) with the strides of
  * b200_per_token_group_quant_fp8 (may be NULL).  Equal, bit for bit when no multicast is involved, to
  * b200_ar_allreduce followed by b200_rmsnorm_quant_fp8.  H % 128 == 0, H <= 8192, M * H * 2 <= max_message_bytes.
- * B200_ERR_UNSUPPORTED where the two separate kernels are the faster plan (more than 4 ranks, measured). */
+ * B200_ERR_UNSUPPORTED where the two separate kernels are the faster plan (more than 4 ranks and H < 8192, measured). */
 int b200_ar_allreduce_add_rmsnorm(void* ctx, const void* in, void* residual, const void* weight, void* norm_out, void* q,
                                   int64_t q_stride_m, float* s, int64_t s_stride_m, int64_t s_stride_g, int M, int H,
                                   int dtype, float eps, float quant_eps, float fp8_min, float fp8_max, void* stream);

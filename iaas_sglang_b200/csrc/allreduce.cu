@@ -672,7 +672,8 @@ extern "C" void b200_ar_destroy(void* ctx) {
 static int ar_policy(int world, size_t bytes, bool fused) {
   if (world < 2 || world > AR_MAX_RANKS) return 0;
   if (world == 2) return 5;
-  if (world <= 4) return bytes <= (fused ? (size_t)1536 << 10 : (size_t)768 << 10) ? 5 : 6;
+  (void)fused;   // 4 ranks, fused 128x5120 (1.3 MB): push-1 15.7, push-2 13.5; 256x4096: 17.9 / 13.3 -- same threshold as plain
+  if (world <= 4) return bytes <= ((size_t)768 << 10) ? 5 : 6;
   return bytes <= ((size_t)512 << 10) ? 5 : 6;
 }
 extern "C" int b200_ar_mode2(int world, size_t bytes, int multicast) {

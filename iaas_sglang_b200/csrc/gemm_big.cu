@@ -559,7 +559,12 @@ int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw,
   if (mode == 0) {
     // 256-wide tiles are the faster pipeline (2112 vs 1880 TFLOP/s at 8192^3) but a skinny problem has too few of them
     // to put every SM's copy engine to work: below ~3/4 of a wave of 256-wide tiles take 128-wide ones
-    if (bn == 0) bn = ((M + GB_BM - 1) / GB_BM) * ((N + 255) / 256) >= 112 ? 256 : 128;
+    // (one row of tiles, M <= 128: HBM-bound, and a wave of 112 .. 147 wide tiles leaves SMs without a stream --
+    // 28672 x 4096 at M = 64: 25.3 us with 224 tiles of 128 against 26.4 with 112 of 256)
+    if (bn == 0) {
+      const int wide = ((M + GB_BM - 1) / GB_BM) * ((N + 255) / 256);
+      bn = wide >= 112 && !(M <= 64 && wide < 148) ? 256 : 128;
+    }
     // knob gb_pair = 4 selects cta_group::2 pairs for fp8 too (measured slower: the per-k-block release crosses the pair)
     if (pair == 4 && M > GB_BM) {
       if (bn == 128) return launch_big_t<0, 2, 128>(a, lda, w, ldw, bp, st);

@@ -50,7 +50,11 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
   return r;
 }
-__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+// .relaxed: the two cluster barriers of the write-out order EXECUTION only (a peer's ring is drained / my outgoing bulk
+// copies have landed); the data itself is ordered by fence.proxy.async + the mbarrier transaction count.  The .release form
+// compiles to MEMBAR.ALL.GPU, which waits for every outstanding global store of the CTA -- measured with the time stamps
+// below: 1.5 us at barrier A and 3 us at barrier B (behind the output stores) of an 11 us kernel.
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) {
   uint32_t r;
@@ -411,22 +415,28 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
       if (S > 1) fence_proxy_async();  // the bulk copies below read these through the async proxy
     }
     if (S > 1) {
+      // send[] is complete for every thread of this CTA (CTA-scope ordering: the cluster barrier below is relaxed)
+      if (warp >= SK_NONEPI) sk_epi_bar_all<GROUPS>();
       if (threadIdx.x == SK_NONEPI * 32) mbar_arrive_expect_tx(xbar, (uint32_t)((S - 1) * mine * SK_BN * 4));  // armed before anyone can send
       __syncwarp();
       cluster_arrive();  // A: every CTA of the cluster has drained its ring and armed its barrier
       cluster_wait();
       SK_STAMP(3);
-      if (threadIdx.x == SK_NONEPI * 32 && !(p.debug & 1)) {
-        for (int o = 0; o < S; ++o) {
-          if (o == rank) continue;
+      // one lane per destination CTA (a single thread looping over the peers took 1.2 us at S = 6)
+      if (warp == SK_NONEPI && !(p.debug & 1)) {
+        const int o = lane;
+        if (o < S && o != rank) {
           const int o0 = o * slice;
           int on = pt - o0;
           on = on < 0 ? 0 : (on > slice ? slice : on);
-          if (on == 0) continue;
-          const int slot = (rank - o - 1 + S) % S;
-          bulk_s2c(mapa_u32(smem_u32(recv + slot * slice * SK_BN), (uint32_t)o), smem_u32(send + o0 * SK_BN),
-                   (uint32_t)(on * SK_BN * 4), mapa_u32(smem_u32(xbar), (uint32_t)o));
+          if (on > 0) {
+            int slot = rank - o - 1;
+            if (slot < 0) slot += S;
+            bulk_s2c(mapa_u32(smem_u32(recv + slot * slice * SK_BN), (uint32_t)o), smem_u32(send + o0 * SK_BN),
+                     (uint32_t)(on * SK_BN * 4), mapa_u32(smem_u32(xbar), (uint32_t)o));
+          }
         }
+        __syncwarp();
       }
       SK_STAMP(4);
       if (warp >= SK_NONEPI && !(p.debug & 1)) mbar_wait(xbar, ps & 1);
@@ -453,18 +463,22 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
           b1 = p.out_bf16 ? half_to_float<true>(u1) : half_to_float<false>(u1);
         }
       }
+      // where the partial of CTA s2 for my first token sits (floats from `send`): no division inside the token loop
+      int poff[SK_MAX_SPLITS];
+#pragma unroll
+      for (int s2 = 0; s2 < SK_MAX_SPLITS; ++s2) {
+        int slot = s2 - rank - 1;
+        if (slot < 0) slot += S;
+        poff[s2] = (s2 == rank ? my0 * SK_BN : (P + slot * slice) * SK_BN) + n_in;
+      }
 #pragma unroll 2
       for (int tk = tq; tk < mine; tk += NE / 64) {
         const int m = t0 + my0 + tk;
         if (m >= p.M || n >= p.N) continue;
         float2 v[SK_MAX_SPLITS];
 #pragma unroll
-        for (int s2 = 0; s2 < SK_MAX_SPLITS; ++s2) {
-          if (s2 < S) {
-            const float* src = s2 == rank ? send + (my0 + tk) * SK_BN : recv + (((s2 - rank - 1 + S) % S) * slice + tk) * SK_BN;
-            v[s2] = *reinterpret_cast<const float2*>(src + n_in);
-          }
-        }
+        for (int s2 = 0; s2 < SK_MAX_SPLITS; ++s2)
+          if (s2 < S) v[s2] = *reinterpret_cast<const float2*>(send + poff[s2] + tk * SK_BN);
         float o0, o1;
         if (MODE != 1) {
           o0 = v[0].x;
@@ -534,16 +548,21 @@ size_t skinny_workspace_bytes(int, int, int) { return 2048 * 8 * 8; }  // (devel
 bool skinny_applicable(int M) { return M <= 256; }
 
 // FP8 block-scaled: skinny (swap-AB, cluster split-K) or the persistent large-M kernel?  Measured policy
-// (tools/kb_cross.py over the TP-local shapes of cfg 2/4/5, profiles/r02_kb_cross.txt): the large-M kernel wins at every
-// M > 128 and wherever the K loop is short (K <= 3584) or there are many n-tiles at K <= 4096; the skinny kernel wins on
-// long-K, few-tile shapes, where its split-K puts every SM to work.  Knob sk_max_m >= 0 forces "skinny iff M <= sk_max_m".
+// (tools/kb_cross.py over the TP-local shapes of cfg 2/4/5 at M 32 / 64 / 128, profiles/r02_kb_cross.txt, second table:
+// after the write-out of this kernel lost its GPU-scope fences and its divisions): the large-M kernel wins at every
+// M > 128, on short K loops (K <= 2304; K <= 1024 at M <= 32), on the widest weights at K <= 4096 (gate_up: 224 tiles
+// of 128 columns stream better from the persistent kernel) and, at 64 < M <= 128, wherever K <= 4096 meets N >= 6144 or
+// K < 4096; the skinny kernel wins everywhere else -- its split-K puts every SM to work on few-tile shapes.
+// Knob sk_max_m >= 0 forces "skinny iff M <= sk_max_m".
 bool skinny_applicable_fp8(int M, int N, int K) {
   const int max_m = tune(TUNE_SK_MAX_M);
   if (max_m >= 0) return M <= (max_m > 256 ? 256 : max_m);
   if (M > 128) return false;
-  if (K <= 3584) return false;
-  if (K <= 4096 && N >= 6144) return false;
-  return true;
+  if (M <= 32) return K >= 1536;
+  if (K <= 2304) return false;
+  if (M <= 64) return !(K <= 4096 && N >= 16384);
+  if (K >= 7168) return true;
+  return K >= 4096 && N <= 4096;
 }
 
 struct SkinnyPlan {
@@ -610,7 +629,9 @@ static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, SkinnyP
   for (int s2 = 2; s2 <= SK_MAX_SPLITS; ++s2) {
     const int slice = (P + s2 - 1) / s2;
     const bool fits = (P + (s2 - 1) * slice) * SK_BN * 4 <= ring_bytes;
-    if (sp.n_tiles * s2 <= capacity[s2] && sp.kb_total / s2 >= 2 && fits && sp.n_tiles * s2 > best) {
+    // (capacity + 1/15: the occupancy API under-counts clusters of 8 -- 32 tiles x 8 = 256 CTAs against an answer of 240
+    // run in one wave, 14.1 us against 16.0 for S = 6 on 4096 x 14336; 48 x 6 = 288 against 264 do not: 14.2 against 9.7 for S = 5)
+    if (sp.n_tiles * s2 <= capacity[s2] + capacity[s2] / 15 && sp.kb_total / s2 >= 2 && fits && sp.n_tiles * s2 > best) {
       S = s2;
       best = sp.n_tiles * s2;
     }

@@ -49,7 +49,8 @@ __device__ __forceinline__ uint32_t aq_cluster_ctarank() {
   return r;
 }
 __device__ __forceinline__ void aq_cluster_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  // .relaxed: these barriers order execution only (see gemm_skinny.cu cluster_arrive: .release is a MEMBAR.ALL.GPU)
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ uint32_t aq_mapa(uint32_t smem_addr, uint32_t rank) {
@@ -321,20 +322,24 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
         if (S > 1) fence_proxy_async();
       }
       if (S > 1) {
+        if (warp >= AQ_NONEPI) aq_epi_bar<GROUPS>();   // send[] complete at CTA scope (the cluster barrier is relaxed)
         if (threadIdx.x == AQ_NONEPI * 32) mbar_arrive_expect_tx(xbar, (uint32_t)((S - 1) * mine * AQ_BN * 4));
         __syncwarp();
         aq_cluster_sync();  // A: partials are in place and every barrier is armed
-        if (threadIdx.x == AQ_NONEPI * 32) {
-          for (int o = 0; o < S; ++o) {
-            if (o == rank) continue;
+        if (warp == AQ_NONEPI) {   // one lane per destination CTA
+          const int o = lane;
+          if (o < S && o != rank) {
             const int o0 = o * slice;
             int on = pt - o0;
             on = on < 0 ? 0 : (on > slice ? slice : on);
-            if (on == 0) continue;
-            const int slot = (rank - o - 1 + S) % S;
-            aq_bulk_s2c(aq_mapa(smem_u32(recv + slot * slice * AQ_BN), (uint32_t)o), smem_u32(send + o0 * AQ_BN),
-                        (uint32_t)(on * AQ_BN * 4), aq_mapa(smem_u32(xbar), (uint32_t)o));
+            if (on > 0) {
+              int slot = rank - o - 1;
+              if (slot < 0) slot += S;
+              aq_bulk_s2c(aq_mapa(smem_u32(recv + slot * slice * AQ_BN), (uint32_t)o), smem_u32(send + o0 * AQ_BN),
+                          (uint32_t)(on * AQ_BN * 4), aq_mapa(smem_u32(xbar), (uint32_t)o));
+            }
           }
+          __syncwarp();
         }
         if (warp >= AQ_NONEPI) mbar_wait(xbar, xph & 1);
         ++xph;
@@ -352,6 +357,13 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
           b0 = half_to_float<BF>(u0);
           b1 = half_to_float<BF>(u1);
         }
+        int poff[AQ_MAX_SPLITS];   // partial of CTA s for my first token (floats from `send`): no division in the token loop
+#pragma unroll
+        for (int s2i = 0; s2i < AQ_MAX_SPLITS; ++s2i) {
+          int slot = s2i - rank - 1;
+          if (slot < 0) slot += S;
+          poff[s2i] = (s2i == rank ? my0 * AQ_BN : (int)(recv - send) + slot * slice * AQ_BN) + (n_in ^ (((n_in >> 5) & 3) << 1));
+        }
 #pragma unroll 2
         for (int tk = tq; tk < mine; tk += NE / 64) {
           const int m = t0 + my0 + tk;
@@ -360,8 +372,7 @@ awq_fused_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constan
 #pragma unroll
           for (int s2i = 0; s2i < AQ_MAX_SPLITS; ++s2i) {
             if (s2i < S) {
-              const float* src = s2i == rank ? send + (my0 + tk) * AQ_BN : recv + (((s2i - rank - 1 + S) % S) * slice + tk) * AQ_BN;
-              const float2 v = *reinterpret_cast<const float2*>(src + (n_in ^ (((n_in >> 5) & 3) << 1)));
+              const float2 v = *reinterpret_cast<const float2*>(send + poff[s2i] + tk * AQ_BN);
               o0 = s2i == 0 ? v.x : o0 + v.x;
               o1 = s2i == 0 ? v.y : o1 + v.y;
             }

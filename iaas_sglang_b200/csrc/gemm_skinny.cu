@@ -442,7 +442,9 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
       if (warp >= SK_NONEPI && !(p.debug & 1)) mbar_wait(xbar, ps & 1);
       SK_STAMP(5);
     } else if (warp >= SK_NONEPI) {
+      SK_STAMP(3);
       sk_epi_bar_all<GROUPS>();
+      SK_STAMP(4);
     }
     // 2. sum the S partials of the owned tokens in CTA order (bit-reproducible), scale (int8), convert, store:
     //    a thread owns two adjacent output columns, a warp writes whole 128-byte lines

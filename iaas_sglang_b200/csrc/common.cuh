@@ -27,7 +27,7 @@ bool pdl_enabled();
 // b200_tune_set / b200_tune_get change them at run time (tools/, tests).
 enum TuneKey {
   TUNE_PDL = 0, TUNE_SK_MAX_M, TUNE_SK_STAGES, TUNE_SK_SPLITS, TUNE_SK_DEBUG, TUNE_GB_PAIR, TUNE_GB_BN, TUNE_GB_PROF,
-  TUNE_AWQ_NT, TUNE_AWQ_SPLITS, TUNE_AWQ_DEBUG, TUNE_AWQ_V1, TUNE_ATTN_BULK_MIN, TUNE_GB_EPI, TUNE_AR_BLOCK_VEC, TUNE_AR_FUSED_WORLD, TUNE_COUNT
+  TUNE_AWQ_NT, TUNE_AWQ_SPLITS, TUNE_AWQ_DEBUG, TUNE_AWQ_V1, TUNE_ATTN_BULK_MIN, TUNE_GB_EPI, TUNE_AR_BLOCK_VEC, TUNE_AR_FUSED_WORLD, TUNE_GB_SPLIT, TUNE_COUNT
 };
 int tune(TuneKey k);
 

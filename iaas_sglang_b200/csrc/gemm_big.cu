@@ -46,6 +46,12 @@ struct BigParams {
   int out_bf16;
   int M, N, K;
   int kb_total, tiles_m, tiles_n, n_tiles, group_m, workers;
+  // split-K (fp8, 128-wide tiles, few tiles): n_units = n_tiles * ksplit <= workers, unit u = (tile u / ksplit, K slice
+  // u % ksplit); the slices of a tile meet in `part` (fp32, [unit][thread][32 float2]) behind two self-resetting counters
+  // per tile in `tickets` (arrived, departed)
+  int ksplit, n_units;
+  int* tickets;
+  float* part;
   long long* prof;  // developer (-DGB_PROF + knob gb_prof): per-CTA clock64 sums of the MMA thread's pipeline waits
 };
 
@@ -227,26 +233,31 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       // weights do not depend on the previous kernel of the stream: the first ring-full of W tiles is requested before
       // griddepcontrol.wait, the activations after it (decode-shape calls: the ramp of this GEMM overlaps its predecessor)
       int pre = 0;
+      const int S = p.ksplit;
       if constexpr (PAIR == 1) {
-        if (worker < p.n_tiles) {
+        if (worker < p.n_units) {
           int tm, tn;
-          gb_tile_coord(p, worker, tm, tn);
-          pre = p.kb_total < stages ? p.kb_total : stages;
+          const int t = worker / S, si = worker - t * S;
+          gb_tile_coord(p, t, tm, tn);
+          const int kb_lo = si * p.kb_total / S, kb_hi = (si + 1) * p.kb_total / S;
+          pre = kb_hi - kb_lo < stages ? kb_hi - kb_lo : stages;
           if (elect_one()) {
-            for (int kb = 0; kb < pre; ++kb) {
-              mbar_arrive_expect_tx(&full[kb], STAGE_BYTES);
-              tma_load_2d(smem + kb * STAGE_BYTES + A_BYTES, &tma_b, kb * GB_BK, tn * GB_BN, &full[kb]);
+            for (int i = 0; i < pre; ++i) {
+              mbar_arrive_expect_tx(&full[i], STAGE_BYTES);
+              tma_load_2d(smem + i * STAGE_BYTES + A_BYTES, &tma_b, (kb_lo + i) * GB_BK, tn * GB_BN, &full[i]);
             }
           }
           __syncwarp();
         }
       }
       griddep_wait();
-      for (int t = worker; t < p.n_tiles; t += p.workers) {
+      for (int u = worker; u < p.n_units; u += p.workers) {
         int tm, tn;
+        const int t = u / S, si = u - t * S;
         gb_tile_coord(p, t, tm, tn);
         const int m0 = (tm * PAIR + rank) * GB_BM, n0 = tn * GB_BN + rank * B_ROWS;
-        for (int kb = 0; kb < p.kb_total; ++kb) {
+        const int kb_lo = si * p.kb_total / S, kb_hi = (si + 1) * p.kb_total / S;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           if (pre > 0) {   // this stage's W tile is already in flight (first tile only): add the activations
             --pre;
             if (elect_one()) tma_load_2d(smem + s * STAGE_BYTES, &tma_a, kb * GB_BK, m0, &full[s]);
@@ -284,12 +295,15 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       long long pm_tempty = 0, pm_full = 0, pm_n = 0;
       const long long pm_t0 = clock64();
 #endif
-      for (int t = worker; t < p.n_tiles; t += p.workers) {
-        for (int kb = 0; kb < p.kb_total; ++kb) {
+      const int S = p.ksplit;
+      for (int u = worker; u < p.n_units; u += p.workers) {
+        const int si = u % S;
+        const int kb_lo = si * p.kb_total / S, kb_hi = (si + 1) * p.kb_total / S;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
 #ifdef GB_PROF
           const long long c0 = clock64();
 #endif
-          if (MODE == 0 || kb == 0) mbar_wait(&tempty[a], aph ^ 1);
+          if (MODE == 0 || kb == kb_lo) mbar_wait(&tempty[a], aph ^ 1);
 #ifdef GB_PROF
           const long long c1 = clock64();
 #endif
@@ -304,11 +318,11 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           const uint64_t adesc = desc0 + (uint64_t)((uint32_t)(s * STAGE_BYTES) >> 4);
           const uint64_t bdesc = adesc + (A_BYTES >> 4);
           const uint32_t d = tmem_base + a * GB_BN;
-          const bool last_kb = kb == p.kb_total - 1;
+          const bool last_kb = kb == kb_hi - 1;
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < GB_BK / 32; ++k) {
-              const uint32_t accum = MODE == 0 ? (k > 0) : (kb > 0 || k > 0);
+              const uint32_t accum = MODE == 0 ? (k > 0) : (kb > kb_lo || k > 0);
               gb_umma<PAIR, MODE>(d, adesc + 2 * k, bdesc + 2 * k, idesc, accum);
             }
             gb_commit<PAIR>(&empty[s]);
@@ -348,8 +362,11 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     };
     int a = 0;
     uint32_t aph = 0;   // TMEM buffer / phase, advanced exactly as the MMA thread advances its own
-    for (int t = worker; t < p.n_tiles; t += p.workers) {
+    const int S = p.ksplit;
+    for (int u = worker; u < p.n_units; u += p.workers) {
       int tm, tn;
+      const int t = u / S, si = u - t * S;
+      const int kb_lo = si * p.kb_total / S, kb_hi = (si + 1) * p.kb_total / S;
       gb_tile_coord(p, t, tm, tn);
       const int row = (tm * PAIR + rank) * GB_BM + row_in_tile;
       const int n0 = tn * GB_BN + cg * 64;
@@ -362,13 +379,14 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         const float* sa_p = p.sa + (int64_t)(row < p.M ? row : 0) * p.sa_sm;
         const float* sb_p = p.sb + (int64_t)(nb_ok ? nb : 0) * p.sb_sn;
         // the scale loads come from an L2 that the TMA ring keeps busy: they are issued two k-blocks ahead
-        float sa0 = __ldg(sa_p), sb0 = __ldg(sb_p);
-        float sa1 = p.kb_total > 1 ? __ldg(sa_p + p.sa_sk) : 0.f, sb1 = p.kb_total > 1 ? __ldg(sb_p + p.sb_sk) : 0.f;
-        for (int kb = 0; kb < p.kb_total; ++kb) {
+        float sa0 = __ldg(sa_p + (int64_t)kb_lo * p.sa_sk), sb0 = __ldg(sb_p + (int64_t)kb_lo * p.sb_sk);
+        float sa1 = kb_lo + 1 < kb_hi ? __ldg(sa_p + (int64_t)(kb_lo + 1) * p.sa_sk) : 0.f;
+        float sb1 = kb_lo + 1 < kb_hi ? __ldg(sb_p + (int64_t)(kb_lo + 1) * p.sb_sk) : 0.f;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           const float sc = sa0 * sb0;
           sa0 = sa1;
           sb0 = sb1;
-          if (kb + 2 < p.kb_total) {
+          if (kb + 2 < kb_hi) {
             sa1 = __ldg(sa_p + (int64_t)(kb + 2) * p.sa_sk);
             sb1 = __ldg(sb_p + (int64_t)(kb + 2) * p.sb_sk);
           }
@@ -445,6 +463,83 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         }
         if (++a == NBUF) { a = 0; aph ^= 1; }
       }
+      if constexpr (MODE == 0 && EW == 8 && PAIR == 1) {
+        if (S > 1) {
+          // ---- split-K: the S slices of tile t meet in global memory; every CTA of the tile then reduces 1/S of it ----
+          // (all S CTAs are resident: n_units <= workers, one unit per CTA -- the wait below cannot deadlock)
+          const int tid = threadIdx.x;   // 0 .. 255: the epilogue warps are warps 0 .. 7
+          float4* part4 = reinterpret_cast<float4*>(p.part);
+          if (row < p.M && n0 < p.N) {
+            float4* mine = part4 + ((size_t)u * 256 + tid) * 16;
+#pragma unroll
+            for (int j4 = 0; j4 < 16; ++j4) mine[j4] = make_float4(acc[2 * j4].x, acc[2 * j4].y, acc[2 * j4 + 1].x, acc[2 * j4 + 1].y);
+          }
+          __threadfence();
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (tid == 0) {
+            int* arrived = p.tickets + 2 * t;
+            asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(arrived) : "memory");   // no return value: one L2 round trip less
+            int seen;
+            do {
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(arrived) : "memory");
+            } while (seen < S);
+          }
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          __threadfence();
+          const int lo = si * 256 / S, hi = (si + 1) * 256 / S;
+          const int row_base = (tm * PAIR + rank) * GB_BM, col_base = tn * GB_BN;
+          uint16_t* outp = reinterpret_cast<uint16_t*>(p.out);
+          const bool vec_out = (p.ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 7) == 0);
+          // all S partials of two output chunks are requested before the first add (a load -> add chain per slice costs an
+          // L2 round trip each: measured 9 us for S = 6)
+          const int nf = (hi - lo) * 16;
+          for (int f0 = tid; f0 < nf; f0 += 512) {
+            float4 v[2][8];
+            bool ok[2];
+            int orow[2], ocol[2];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+              const int f = f0 + q * 256;
+              const int owner = lo + (f >> 4), j4 = f & 15;
+              const int ow = owner >> 5;   // owner's warp: TMEM lane quarter ow & 3, column group ow >> 2
+              orow[q] = row_base + (ow & 3) * 32 + (owner & 31);
+              ocol[q] = col_base + (ow >> 2) * 64 + 4 * j4;
+              ok[q] = f < nf && orow[q] < p.M && col_base + (ow >> 2) * 64 < p.N;
+#pragma unroll
+              for (int s2 = 0; s2 < 8; ++s2)
+                if (ok[q] && s2 < S) v[q][s2] = __ldcg(part4 + ((size_t)(t * S + s2) * 256 + owner) * 16 + j4);
+            }
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+              if (!ok[q]) continue;
+              float4 sum = v[q][0];
+#pragma unroll
+              for (int s2 = 1; s2 < 8; ++s2)   // fixed order: bit-reproducible whoever arrives last
+                if (s2 < S) { sum.x += v[q][s2].x; sum.y += v[q][s2].y; sum.z += v[q][s2].z; sum.w += v[q][s2].w; }
+              uint16_t* dst = outp + (size_t)orow[q] * p.ldo + ocol[q];
+              if (vec_out && ocol[q] + 4 <= p.N) {
+                uint2 pk;
+                if (p.out_bf16) { pk.x = pack_half2<true>(sum.x, sum.y); pk.y = pack_half2<true>(sum.z, sum.w); }
+                else { pk.x = pack_half2<false>(sum.x, sum.y); pk.y = pack_half2<false>(sum.z, sum.w); }
+                *reinterpret_cast<uint2*>(dst) = pk;
+              } else {
+                const float o4[4] = {sum.x, sum.y, sum.z, sum.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                  if (ocol[q] + e < p.N) dst[e] = p.out_bf16 ? float_to_half<true>(o4[e]) : float_to_half<false>(o4[e]);
+              }
+            }
+          }
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (tid == 0) {   // the last CTA to leave re-arms the tile's counters for the next call
+            if (atomicAdd(p.tickets + 2 * t + 1, 1) == S - 1) {
+              p.tickets[2 * t] = 0;
+              p.tickets[2 * t + 1] = 0;
+            }
+          }
+          continue;
+        }
+      }
       // ---- write 64 output columns of this thread's row ----
       if (row < p.M && n0 < p.N) {
         uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + (size_t)row * p.ldo + n0;
@@ -482,8 +577,12 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   }
 }
 
+constexpr size_t GB_TICKET_BYTES = 4096;            // two counters per tile, <= 512 tiles
+constexpr size_t GB_PART_BYTES = 256 * 32 * 8;      // one unit's fp32 partial tile: 256 threads x 32 float2
+
 template <int MODE, int PAIR, int BN>
-static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, BigParams& bp, cudaStream_t st) {
+static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, BigParams& bp, void* workspace,
+                        size_t workspace_bytes, cudaStream_t st) {
   constexpr int GB_BN = BN, GB_THREADS = (4 + BN / 16) * 32;
   constexpr int STAGE_BYTES = GB_BM * GB_BK + (GB_BN / PAIR) * GB_BK;
   const int stages = (226 * 1024 - 1024 - 512) / STAGE_BYTES > GB_MAX_STAGES ? GB_MAX_STAGES : (226 * 1024 - 1024 - 512) / STAGE_BYTES;
@@ -494,9 +593,33 @@ static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, 
   bp.n_tiles = bp.tiles_m * bp.tiles_n;
   bp.group_m = 16 / PAIR;
   const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
+  // split-K where the tiles fill less than half of the SMs (fp8, 128-wide tiles, large-M kernel chosen: M > 128 or a short
+  // K loop): a CTA streams at most ~100 GB/s, so 24 tiles of a 1536 x 4096 weight keep 24 SMs busy for 13 us whatever the
+  // HBM could do; S slices per tile put S times the SMs on the same bytes.  A function of the shape only (the TP
+  // emulation of bench.py and the fused / unfused parity tests rely on that); knob gb_split: 0 auto, 1 off, n forces n.
+  int S = 1;
+  if (MODE == 0 && PAIR == 1 && BN == 128 && workspace && ((uintptr_t)workspace & 15) == 0 && bp.n_tiles * 2 <= sms &&
+      (size_t)bp.n_tiles * 8 <= GB_TICKET_BYTES) {
+    const int knob = tune(TUNE_GB_SPLIT);
+    S = sms / bp.n_tiles;
+    if (S > 8) S = 8;
+    if (S > bp.kb_total / 4) S = bp.kb_total / 4;   // >= 4 k-blocks per slice
+    // the slices meet through L2 (partial tile, fence, counter, wait, reload: ~5 us of round trips, tools/gb_split_sweep.py),
+    // a CTA spends ~0.3 us per k-block: worth it only if the k-loop shrinks by more than that -- measured: K = 8192 with 20
+    // tiles 22.0 -> 13.0 us, K = 7168 with 34 tiles 20.3 -> 14.1, K = 4096 with 24 tiles 13.0 -> 11.7; K <= 3584 loses
+    if (S > 1 && bp.kb_total * (S - 1) < 24 * S) S = 1;
+    if (knob > 0) S = knob;
+    if (S > bp.kb_total) S = bp.kb_total;
+    while (S > 1 && (bp.n_tiles * S > sms || GB_TICKET_BYTES + (size_t)bp.n_tiles * S * GB_PART_BYTES > workspace_bytes)) --S;
+    if (S < 1) S = 1;
+  }
+  bp.ksplit = S;
+  bp.n_units = bp.n_tiles * S;
+  bp.tickets = S > 1 ? reinterpret_cast<int*>(workspace) : nullptr;
+  bp.part = S > 1 ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + GB_TICKET_BYTES) : nullptr;
   int workers = sms / PAIR;
-  if (workers > bp.n_tiles) workers = bp.n_tiles;
-  bp.workers = workers;
+  if (workers > bp.n_units) workers = bp.n_units;
+  bp.workers = workers;   // (S > 1: n_units <= sms, every unit has its own resident CTA)
   CUtensorMap ta, tb;
   if (int rc = make_tmap_2d(&ta, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, bp.M, bp.K, lda, GB_BM, GB_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
   if (int rc = make_tmap_2d(&tb, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, bp.N, bp.K, ldw, GB_BN / PAIR, GB_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
@@ -546,9 +669,14 @@ static int launch_big_t(const void* a, int64_t lda, const void* w, int64_t ldw, 
 }
 
 // a [M,K] activations, w [N,K] weight (both K-major, 1-byte elements); mode 0 fp8 block-scaled, 1 int8
+size_t big_workspace_bytes() {
+  const int sms = device_sm_count() > 0 ? device_sm_count() : 148;
+  return GB_TICKET_BYTES + (size_t)sms * GB_PART_BYTES;
+}
+
 int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw, const float* sa, int64_t sa_sm, int64_t sa_sk,
                const float* sb, int64_t sb_sk, int64_t sb_sn, const void* bias, void* out, int64_t ldo, int out_bf16, int M,
-               int N, int K, cudaStream_t st) {
+               int N, int K, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   BigParams bp{};
   bp.sa = sa; bp.sa_sm = sa_sm; bp.sa_sk = sa_sk;
   bp.sb = sb; bp.sb_sk = sb_sk; bp.sb_sn = sb_sn;
@@ -567,14 +695,14 @@ int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw,
     }
     // knob gb_pair = 4 selects cta_group::2 pairs for fp8 too (measured slower: the per-k-block release crosses the pair)
     if (pair == 4 && M > GB_BM) {
-      if (bn == 128) return launch_big_t<0, 2, 128>(a, lda, w, ldw, bp, st);
-      return launch_big_t<0, 2, 256>(a, lda, w, ldw, bp, st);
+      if (bn == 128) return launch_big_t<0, 2, 128>(a, lda, w, ldw, bp, workspace, workspace_bytes, st);
+      return launch_big_t<0, 2, 256>(a, lda, w, ldw, bp, workspace, workspace_bytes, st);
     }
-    if (bn == 128) return launch_big_t<0, 1, 128>(a, lda, w, ldw, bp, st);
-    return launch_big_t<0, 1, 256>(a, lda, w, ldw, bp, st);
+    if (bn == 128) return launch_big_t<0, 1, 128>(a, lda, w, ldw, bp, workspace, workspace_bytes, st);
+    return launch_big_t<0, 1, 256>(a, lda, w, ldw, bp, workspace, workspace_bytes, st);
   }
-  if (pair != 1 && M > GB_BM) return launch_big_t<1, 2, 256>(a, lda, w, ldw, bp, st);
-  return launch_big_t<1, 1, 256>(a, lda, w, ldw, bp, st);
+  if (pair != 1 && M > GB_BM) return launch_big_t<1, 2, 256>(a, lda, w, ldw, bp, workspace, workspace_bytes, st);
+  return launch_big_t<1, 1, 256>(a, lda, w, ldw, bp, workspace, workspace_bytes, st);
 }
 
 }  // namespace b200

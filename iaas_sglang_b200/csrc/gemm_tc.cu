@@ -28,7 +28,8 @@ namespace b200 {
 // gemm_big.cu: persistent 256-wide-tile kernel for M > 256 (mode 0 fp8 block-scaled, 1 int8)
 int launch_big(int mode, const void* a, int64_t lda, const void* w, int64_t ldw, const float* sa, int64_t sa_sm, int64_t sa_sk,
                const float* sb, int64_t sb_sk, int64_t sb_sn, const void* bias, void* out, int64_t ldo, int out_bf16, int M,
-               int N, int K, cudaStream_t st);
+               int N, int K, void* workspace, size_t workspace_bytes, cudaStream_t st);
+size_t big_workspace_bytes();
 
 constexpr int BM = 128, BN = 128, BKB = 128;  // BKB: bytes (== elements) of K per stage
 constexpr int kStages = 6;
@@ -350,10 +351,12 @@ using namespace b200;
 
 extern "C" size_t b200_gemm_workspace_size(int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 16;
-  if (skinny_applicable(M)) return skinny_workspace_bytes(M, N, K);
+  // the large-M fp8 kernel splits K on few-tile shapes (gemm_big.cu): tickets + one fp32 partial tile per SM
+  const size_t big = big_workspace_bytes();
+  if (skinny_applicable(M)) return skinny_workspace_bytes(M, N, K) > big ? skinny_workspace_bytes(M, N, K) : big;
   const SplitPlan sp = plan_split(M, N, K);
-  if (sp.splits <= 1) return 16;
-  return kCounterBytes + (size_t)sp.tiles_m * sp.tiles_n * sp.splits * BM * BN * 4;
+  const size_t old_plan = sp.splits <= 1 ? 16 : kCounterBytes + (size_t)sp.tiles_m * sp.tiles_n * sp.splits * BM * BN * 4;
+  return old_plan > big ? old_plan : big;
 }
 
 extern "C" int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
@@ -380,7 +383,7 @@ extern "C" int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const vo
     return launch_skinny<0>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
   }
   return launch_big(0, a, lda, b, ldb, sa, sa_sm, sa_sk, sb, sb_sk, sb_sn, nullptr, out, ldo, out_dtype == B200_BF16, M, N, K,
-                    (cudaStream_t)stream);
+                    workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 namespace b200 {
@@ -419,5 +422,6 @@ extern "C" int b200_int8_scaled_mm(const void* a, int64_t lda, const void* b, in
     sp.M = M; sp.N = N; sp.K = K;
     return launch_skinny<1>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
   }
-  return launch_big(1, a, lda, b, ldb, sa, 0, 0, sb, 0, 0, bias, out, ldo, out_dtype == B200_BF16, M, N, K, (cudaStream_t)stream);
+  return launch_big(1, a, lda, b, ldb, sa, 0, 0, sb, 0, 0, bias, out, ldo, out_dtype == B200_BF16, M, N, K, nullptr, 0,
+                    (cudaStream_t)stream);
 }

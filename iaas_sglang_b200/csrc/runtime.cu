@@ -49,6 +49,7 @@ static const TuneEntry kTune[TUNE_COUNT] = {
     {"gb_epi", "B200_GB_EPI", 0},
     {"ar_block_vec", "B200_AR_BLOCK_VEC", 0},   // push all-reduce: 16-byte vectors per block (0 = 256: one row per block); same on every rank
     {"ar_fused_world", "B200_AR_FUSED_WORLD", 4},   // largest world size at which all-reduce + add + RMSNorm runs as ONE kernel
+    {"gb_split", "B200_GB_SPLIT", 0},   // large-M fp8 kernel, few-tile shapes: K slices per tile (0 = by shape, 1 = off)
 };
 static int g_tune[TUNE_COUNT];
 static const bool g_tune_loaded = [] {

@@ -78,6 +78,35 @@ def test_fp8_blockwise_tp_shapes_on_both_kernels(M, N, K):
         _lib.tune_set("sk_max_m", old)
 
 
+@pytest.mark.parametrize("M,N,K,split", [(200, 1280, 8192, 0), (256, 1288, 8192, 7), (130, 2112, 7168, 4), (512, 768, 4096, 6),
+                                         (129, 520, 2048, 3), (256, 4096, 1024, 2)])
+def test_fp8_large_m_kernel_split_k(M, N, K, split):
+    """The large-M kernel's split-K (few-tile shapes: K slices meet in the zero-initialised workspace behind self-resetting
+    counters): right against the oracle, bit-reproducible from call to call (fixed summation order), and the counters are
+    back at zero afterwards (the unsplit kernel and other shapes share the workspace).  Ragged M and N, forced and automatic
+    slice counts (knob gb_split)."""
+    from iaas_sglang_b200 import _lib
+
+    a, b, sa, sb = make_fp8_gemm_case(M, N, K, seed=M + N + K, dist="realistic")
+    ref = orc.fp8_blockwise_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    old_m, old_s = _lib.tune_get("sk_max_m"), _lib.tune_get("gb_split")
+    try:
+        _lib.tune_set("sk_max_m", 0)      # large-M kernel whatever M
+        _lib.tune_set("gb_split", 1)
+        plain = _run_fp8(a, b, sa, sb)
+        _lib.tune_set("gb_split", split)
+        outs = [_run_fp8(a, b, sa, sb) for _ in range(3)]
+        torch.cuda.synchronize()
+        assert rel_l2(outs[0], ref) < 1e-3, rel_l2(outs[0], ref)
+        assert rel_l2(outs[0], plain) < 1e-3
+        assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+        _lib.tune_set("gb_split", 1)
+        assert torch.equal(_run_fp8(a, b, sa, sb), plain)
+    finally:
+        _lib.tune_set("sk_max_m", old_m)
+        _lib.tune_set("gb_split", old_s)
+
+
 def test_fp8_blockwise_fp16_out_and_preconditions():
     from iaas_sglang_b200 import ops
 

@@ -20,19 +20,26 @@ fp8_dtype = torch.float8_e4m3fn
 FP8_MAX = 448.0
 
 # ---------------------------------------------------------------------------------------------
-# scratch: one zero-initialised split-K workspace per device (tile tickets are self-resetting)
+# scratch: one zero-initialised split-K workspace per (device, stream) -- GEMMs that run concurrently on two streams
+# must not share one (partial tiles and tile counters live there, b200_sgl.h); the counters are self-resetting
 # ---------------------------------------------------------------------------------------------
-_gemm_ws: Dict[torch.device, torch.Tensor] = {}
+_gemm_ws: Dict[Tuple[torch.device, int], torch.Tensor] = {}
 
 
 def gemm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    ws = _gemm_ws.get(device)
+    key = (device, int(torch.cuda.current_stream(device).cuda_stream))
+    ws = _gemm_ws.get(key)
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():
+            # a capture stream that never ran eagerly: share a workspace of this device (graphs of one device replay in
+            # stream order unless the caller overlaps them -- then reserve one per stream before capturing)
+            for (d, _), w in _gemm_ws.items():
+                if d == device and w.numel() >= nbytes:
+                    return w
             raise RuntimeError("iaas_sglang_b200: GEMM workspace must be sized before CUDA-graph capture "
                                "(call ops.reserve_gemm_workspace)")
         ws = torch.zeros(max(nbytes, 32 << 20), dtype=torch.uint8, device=device)
-        _gemm_ws[device] = ws
+        _gemm_ws[key] = ws
     return ws
 
 

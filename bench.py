@@ -372,9 +372,14 @@ class DecodeStack(StackBase):
         from iaas_sglang_b200 import ops
 
         d = self.d
-        qkv = self.method.apply_quantized(self.w_qkv[l], x[0], x[1], self.dtype) if fused else self.method.apply(self.w_qkv[l], x)
-        q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
-        ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
+        if fused:   # RoPE in the qkv GEMM's epilogue where the decode-shape kernel serves the shape (same bits, one launch less)
+            qkv = self.method.apply_quantized(self.w_qkv[l], x[0], x[1], self.dtype,
+                                              rope=(self.positions, (self.hq + self.hkv) * d, d, self.wl["theta"], self.rope_cs))
+            q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)   # strided views, no copies
+        else:
+            qkv = self.method.apply(self.w_qkv[l], x)
+            q, k, v = qkv.split([self.hq * d, self.hkv * d, self.hkv * d], dim=-1)
+            ops.rope_neox_(q, k, self.positions, d, self.wl["theta"])
         if fused:   # the attention merge kernel emits the group-128 quantisation of its output itself
             a = self.attn[l](q, k, v, self.fb, quant_fp8=True)
             return self.method.apply_quantized(self.w_o[l], a[0], a[1], self.dtype)
@@ -392,9 +397,13 @@ class DecodeStack(StackBase):
 
     def forward(self) -> torch.Tensor:
         """One decode step over the static buffers (eager; also the body that gets graph-captured)."""
+        from iaas_sglang_b200 import ops
+
         h = self.hidden_in
         residual = torch.zeros_like(h)
         fused = hasattr(self.method, "apply_quantized") and not self.no_fused
+        # the rotary cos / sin rows of this step's positions, once for all layers (the qkv GEMM's epilogue rotates with them)
+        self.rope_cs = ops.rope_cos_sin(self.positions, self.d, self.wl["theta"]) if fused and self.d == 128 else None
         for l in range(self.L):
             # FP8: the norm / activation / all-reduce kernels emit the group-128 quantisation themselves (bit-identical)
             x = self._norm(h, self.norm1[l], residual, reduce=l > 0, quant=fused)   # residual += [allreduce](h) ; x = norm(residual)

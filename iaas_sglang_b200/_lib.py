@@ -103,6 +103,10 @@ SIGNATURES = {
     "b200_fp8_blockwise_scaled_mm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p,
                                              c_int64, c_int64, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p,
                                              c_size_t, c_void_p]),
+    "b200_fp8_blockwise_scaled_mm_rope": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p,
+                                                  c_int64, c_int64, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p,
+                                                  c_int, c_int, c_void_p, c_size_t, c_void_p]),
+    "b200_rope_cos_sin": (c_int, [c_void_p, c_int, c_int, c_float, c_void_p, c_void_p]),
     "b200_int8_scaled_mm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
                                     c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b200_awq_dequantize": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

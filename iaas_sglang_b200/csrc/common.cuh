@@ -349,4 +349,14 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 #endif  // __CUDACC__
 
+// neox rotary embedding, shared by rope_neox_kernel (elementwise.cu) and the qkv GEMM's fused epilogue (gemm_skinny.cu): the
+// same un-contracted operations in both, hence the same bits (rotary_embedding.py forward_native, is_neox_style)
+__device__ __forceinline__ void rope_sincos(float pos, int i, int D, float log2_theta, float& sn, float& cs) {
+  const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
+  sincosf(__fmul_rn(pos, inv_freq), &sn, &cs);
+}
+// (x1, x2) = columns (i, i + D / 2) of a head: new column i / new column i + D / 2
+__device__ __forceinline__ float rope_lo(float x1, float x2, float cs, float sn) { return __fsub_rn(__fmul_rn(x1, cs), __fmul_rn(x2, sn)); }
+__device__ __forceinline__ float rope_hi(float x1, float x2, float cs, float sn) { return __fadd_rn(__fmul_rn(x2, cs), __fmul_rn(x1, sn)); }
+
 }  // namespace b200

@@ -228,20 +228,18 @@ __global__ void rope_neox_kernel(uint16_t* __restrict__ q, int64_t q_sm, uint16_
     for (int e = threadIdx.x; e < total; e += blockDim.x) {
       const int h = e / half, i = e % half;
       uint16_t* base = h < Hq ? q + (int64_t)m * q_sm + h * D : k + (int64_t)m * k_sm + (h - Hq) * D;
-      const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
       float sn, cs;
-      sincosf(ps * inv_freq, &sn, &cs);
+      rope_sincos(ps, i, D, log2_theta, sn, cs);
       const float x1 = half_to_float<BF16>(base[i]), x2 = half_to_float<BF16>(base[i + half]);
-      base[i] = float_to_half<BF16>(x1 * cs - x2 * sn);
-      base[i + half] = float_to_half<BF16>(x2 * cs + x1 * sn);
+      base[i] = float_to_half<BF16>(rope_lo(x1, x2, cs, sn));
+      base[i + half] = float_to_half<BF16>(rope_hi(x1, x2, cs, sn));
     }
     return;
   }
   const int i = threadIdx.x % half, slot = threadIdx.x / half;
   if (slot >= slots) return;
-  const float inv_freq = exp2f(-log2_theta * (2.f * i) / (float)D);
   float sn, cs;
-  sincosf(ps * inv_freq, &sn, &cs);
+  rope_sincos(ps, i, D, log2_theta, sn, cs);
   // blockIdx.y splits the heads so that a decode batch (M = 64 tokens) still fills the SMs; two heads per trip keep
   // four independent loads in flight per thread
   const int step = slots * gridDim.y;
@@ -251,16 +249,16 @@ __global__ void rope_neox_kernel(uint16_t* __restrict__ q, int64_t q_sm, uint16_
     uint16_t *ba = row(h), *bb = row(h + step);
     const float a1 = half_to_float<BF16>(ba[i]), a2 = half_to_float<BF16>(ba[i + half]);
     const float b1 = half_to_float<BF16>(bb[i]), b2 = half_to_float<BF16>(bb[i + half]);
-    ba[i] = float_to_half<BF16>(a1 * cs - a2 * sn);
-    ba[i + half] = float_to_half<BF16>(a2 * cs + a1 * sn);
-    bb[i] = float_to_half<BF16>(b1 * cs - b2 * sn);
-    bb[i + half] = float_to_half<BF16>(b2 * cs + b1 * sn);
+    ba[i] = float_to_half<BF16>(rope_lo(a1, a2, cs, sn));
+    ba[i + half] = float_to_half<BF16>(rope_hi(a1, a2, cs, sn));
+    bb[i] = float_to_half<BF16>(rope_lo(b1, b2, cs, sn));
+    bb[i + half] = float_to_half<BF16>(rope_hi(b1, b2, cs, sn));
   }
   if (h < Hq + Hkv) {
     uint16_t* base = row(h);
     const float x1 = half_to_float<BF16>(base[i]), x2 = half_to_float<BF16>(base[i + half]);
-    base[i] = float_to_half<BF16>(x1 * cs - x2 * sn);
-    base[i + half] = float_to_half<BF16>(x2 * cs + x1 * sn);
+    base[i] = float_to_half<BF16>(rope_lo(x1, x2, cs, sn));
+    base[i + half] = float_to_half<BF16>(rope_hi(x1, x2, cs, sn));
   }
 }
 
@@ -387,6 +385,29 @@ extern "C" int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int
   else
     launch_pdl(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const uint16_t*)x, (uint16_t*)out, M, d);
   return launched("silu_mul_kernel launch");
+}
+
+// cos_sin[m][i] = (cos, sin)(positions[m] * theta^(-2 i / D)), i < D / 2: the values rope_neox_kernel evaluates per layer,
+// once per decode step (positions are the same for every layer) for the qkv GEMM's fused RoPE epilogue
+__global__ void rope_cos_sin_kernel(const int64_t* __restrict__ pos, int M, int half, float log2_theta, float2* __restrict__ out) {
+  griddep_wait();
+  griddep_launch();
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= M * half) return;
+  const int m = e / half, i = e - m * half;
+  float sn, cs;
+  rope_sincos((float)pos[m], i, 2 * half, log2_theta, sn, cs);
+  out[e] = make_float2(cs, sn);
+}
+
+extern "C" int b200_rope_cos_sin(const int64_t* positions, int M, int head_dim, float theta, float* cos_sin, void* stream) {
+  B200_REQUIRE(positions && cos_sin && M >= 0 && head_dim >= 2 && head_dim % 2 == 0 && theta > 0.f, B200_ERR_ARG, "rope_cos_sin: bad argument");
+  if (M == 0) return B200_OK;
+  if (int rc = require_sm100("rope_cos_sin")) return rc;
+  const int n = M * (head_dim / 2);
+  launch_pdl(rope_cos_sin_kernel, dim3((n + 255) / 256), dim3(256), 0, (cudaStream_t)stream, positions, M, head_dim / 2, log2f(theta),
+             reinterpret_cast<float2*>(cos_sin));
+  return launched("rope_cos_sin_kernel launch");
 }
 
 extern "C" int b200_rope_neox(void* q, int64_t q_sm, void* k, int64_t k_sm, const int64_t* positions, int dtype, int M, int Hq, int Hkv, int D,

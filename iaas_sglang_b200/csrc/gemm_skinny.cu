@@ -78,6 +78,49 @@ __device__ __forceinline__ unsigned long long gtimer() {
     if (p.stamps && threadIdx.x == SK_NONEPI * 32) p.stamps[(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (i)] = gtimer(); \
   } while (0)
 
+// Write-out of a qkv tile with fused neox RoPE (this tile is one q / k head: head_dim == SK_BN).  A thread also sums its
+// PARTNER columns (n_in ^ 64), rounds both pairs to the output type -- what the plain GEMM would have stored and
+// rope_neox_kernel read back -- and rotates with the helpers that kernel uses: same bits, one launch less.  cos / sin come
+// from a per-step table (rope_cos_sin_kernel: the same rope_sincos, once per decode step instead of once per layer); with
+// sincosf inlined here its large-argument path cost a stack frame and spills, and the GEMM lost half its speed.
+__device__ __forceinline__ void sk_rope_store(const SkinnyParams& p, const float* send, int rank, int S, int my0, int P, int slice,
+                                           int mine, int t0, int tq, int tstep, int n_in, int n, bool pair_ok) {
+  constexpr int half = SK_BN / 2;
+  const int i0 = n_in & (half - 1), pdelta = (n_in ^ half) - n_in;
+  for (int tk = tq; tk < mine; tk += tstep) {
+    const int m = t0 + my0 + tk;
+    if (m >= p.M || n >= p.N) continue;
+    // partial of CTA s2 (same slots and the same summation order as the plain write-out; no arrays: this instantiation must
+    // stay free of spills -- a stack frame cost the whole kernel 10 us)
+    float o0 = 0.f, o1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int s2 = 0; s2 < SK_MAX_SPLITS; ++s2) {
+      if (s2 < S) {
+        int slot = s2 - rank - 1;
+        if (slot < 0) slot += S;
+        const float* src = send + (s2 == rank ? my0 * SK_BN : (P + slot * slice) * SK_BN) + n_in + tk * SK_BN;
+        const float2 v = *reinterpret_cast<const float2*>(src), w = *reinterpret_cast<const float2*>(src + pdelta);
+        if (s2 == 0) { o0 = v.x; o1 = v.y; q0 = w.x; q1 = w.y; }
+        else { o0 += v.x; o1 += v.y; q0 += w.x; q1 += w.y; }
+      }
+    }
+    auto rt = [&](float x) { return p.out_bf16 ? half_to_float<true>(float_to_half<true>(x)) : half_to_float<false>(float_to_half<false>(x)); };
+    o0 = rt(o0); o1 = rt(o1); q0 = rt(q0); q1 = rt(q1);
+    const float4 cs4 = __ldg(reinterpret_cast<const float4*>(p.rope_cs + (size_t)m * half + i0));   // i0 is even
+    const float cs0 = cs4.x, sn0 = cs4.y, cs1 = cs4.z, sn1 = cs4.w;
+    float r0, r1;
+    if (n_in < half) { r0 = rope_lo(o0, q0, cs0, sn0); r1 = rope_lo(o1, q1, cs1, sn1); }
+    else { r0 = rope_hi(q0, o0, cs0, sn0); r1 = rope_hi(q1, o1, cs1, sn1); }
+    uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + (size_t)m * p.ldo + n;
+    if (pair_ok) {
+      *reinterpret_cast<uint32_t*>(dst) = p.out_bf16 ? pack_half2<true>(r0, r1) : pack_half2<false>(r0, r1);
+    } else {
+      dst[0] = p.out_bf16 ? float_to_half<true>(r0) : float_to_half<false>(r0);
+      if (n + 1 < p.N) dst[1] = p.out_bf16 ? float_to_half<true>(r1) : float_to_half<false>(r1);
+    }
+  }
+}
+
 template <int GROUPS>
 __device__ __forceinline__ void sk_epi_bar_all() {
   asm volatile("bar.sync 1, %0;" ::"n"(GROUPS * 128) : "memory");
@@ -157,7 +200,7 @@ __device__ __forceinline__ void awq_dequant_stages(const SkinnyParams& p, uint8_
   }
 }
 
-template <int MODE, int COLS, int GROUPS>
+template <int MODE, int COLS, int GROUPS, bool ROPE = false>
 // (M <= 64: small enough in registers and shared memory for two CTAs per SM -- the prologue and write-out of one
 // overlap the streaming of the other, also across consecutive launches)
 __global__ void __launch_bounds__((SK_NONEPI + 4 * GROUPS) * 32, (COLS * GROUPS <= 64) ? 2 : 1)
@@ -473,6 +516,14 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
         if (slot < 0) slot += S;
         poff[s2] = (s2 == rank ? my0 * SK_BN : (P + slot * slice) * SK_BN) + n_in;
       }
+      bool roped = false;
+      if constexpr (ROPE) {
+        if (tile * SK_BN < p.rope_cols) {
+          sk_rope_store(p, send, rank, S, my0, P, slice, mine, t0, tq, NE / 64, n_in, n, pair_ok);
+          roped = true;
+        }
+      }
+      if (!roped) {
 #pragma unroll 2
       for (int tk = tq; tk < mine; tk += NE / 64) {
         const int m = t0 + my0 + tk;
@@ -518,6 +569,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_const
           dst[0] = p.out_bf16 ? float_to_half<true>(o0) : float_to_half<false>(o0);
           if (n + 1 < p.N) dst[1] = p.out_bf16 ? float_to_half<true>(o1) : float_to_half<false>(o1);
         }
+      }
       }
     }
     if (S > 1) {
@@ -588,9 +640,9 @@ static SkinnyPlan skinny_plan(int mode, int mt_pad) {
   return pl;
 }
 
-template <int MODE, int COLS, int GROUPS>
+template <int MODE, int COLS, int GROUPS, bool ROPE = false>
 static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, SkinnyParams& sp, int smem, cudaStream_t st) {
-  auto kern = gemm_skinny_kernel<MODE, COLS, GROUPS>;
+  auto kern = gemm_skinny_kernel<MODE, COLS, GROUPS, ROPE>;
   constexpr int kThreads = (SK_NONEPI + 4 * GROUPS) * 32;
   static bool configured = false;
   static int capacity[SK_MAX_SPLITS + 1] = {0};  // CTAs that can be resident at once with clusters of S = 1..8
@@ -706,6 +758,13 @@ int launch_skinny(const void* a, int64_t lda, const void* w, int64_t ldw, Skinny
   } else {
     if (int rc = make_tmap_2d(&tw, w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.N, sp.K, ldw, SK_BN, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
     if (int rc = make_tmap_2d(&tx, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, sp.M, sp.K, lda, sp.mt_pad, SK_BK, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+  }
+  if constexpr (MODE == 0) {
+    if (sp.rope_cs) {   // qkv projection with fused RoPE: its own instantiations
+      if (sp.mt_pad <= 64) return launch_skinny_t<MODE, 32, 2, true>(tw, tx, sp, pl.smem, st);
+      if (sp.mt_pad <= 128) return launch_skinny_t<MODE, 32, 4, true>(tw, tx, sp, pl.smem, st);
+      return launch_skinny_t<MODE, 64, 4, true>(tw, tx, sp, pl.smem, st);
+    }
   }
   if (sp.mt_pad <= 64) return launch_skinny_t<MODE, 32, 2>(tw, tx, sp, pl.smem, st);
   if (sp.mt_pad <= 128) return launch_skinny_t<MODE, 32, 4>(tw, tx, sp, pl.smem, st);

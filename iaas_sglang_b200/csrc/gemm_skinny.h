@@ -22,6 +22,10 @@ struct SkinnyParams {
   int splits;   // CTAs per cluster = K slices per n-tile (1, 2, 4 or 8)
   int stages;   // depth of the TMA ring
   int tab_cap;  // MODE 0: k-blocks per chunk of the shared-memory scale table
+  // fused neox RoPE on the first rope_cols output columns (q and k heads of a qkv projection; head_dim == the 128-column
+  // tile): rope_cs[m][i] = (cos, sin) of token m's position times frequency i (b200_rope_cos_sin), nullptr = plain GEMM
+  const float2* rope_cs;
+  int rope_cols;
   unsigned long long* stamps;  // developer: per-CTA %globaltimer stamps (B200_SK_DEBUG & 256)
   int debug;    // developer knobs (B200_SK_DEBUG): 1 skip the DSMEM scatter, 2 skip the whole exchange, 4 skip the final sum
 };

@@ -386,6 +386,37 @@ extern "C" int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const vo
                     workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
+// qkv projection + neox RoPE in one launch (fused steps either side of the hot kernels): the first
+// rope_cols output columns are q and k heads of head_dim columns each, rotated by token m's cos / sin row (b200_rope_cos_sin)
+// exactly as b200_rope_neox would rotate the stored GEMM output (same helpers, same bits).  Served by the decode-shape kernel's write-out, where a
+// head is one 128-column tile: B200_ERR_UNSUPPORTED for any other head_dim, or where the measured policy gives this
+// (M, N, K) to the large-M kernel -- the caller then runs the two launches.
+extern "C" int b200_fp8_blockwise_scaled_mm_rope(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
+                                                 int64_t sa_sm, int64_t sa_sk, const float* sb, int64_t sb_sk, int64_t sb_sn,
+                                                 void* out, int64_t ldo, int out_dtype, int M, int N, int K,
+                                                 const float* cos_sin, int rope_cols, int head_dim,
+                                                 void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(a && b && sa && sb && out && cos_sin && ((uintptr_t)cos_sin & 15) == 0, B200_ERR_ARG, "fp8_blockwise_scaled_mm_rope: null or misaligned tensor");
+  B200_REQUIRE(M >= 0 && N > 0 && K > 0 && rope_cols >= 0 && rope_cols <= N, B200_ERR_ARG, "fp8_blockwise_scaled_mm_rope: bad sizes");
+  B200_REQUIRE(out_dtype == B200_BF16 || out_dtype == B200_F16, B200_ERR_ARG, "fp8_blockwise_scaled_mm_rope: out_dtype must be Half or BFloat16");
+  B200_REQUIRE(K % 16 == 0 && (N * 2) % 16 == 0 && lda % 16 == 0 && ldb % 16 == 0, B200_ERR_ARG, "fp8_blockwise_scaled_mm_rope: 16-byte alignment of K, N and the pitches");
+  B200_REQUIRE(head_dim == 128 && rope_cols % 128 == 0, B200_ERR_UNSUPPORTED,
+               "fp8_blockwise_scaled_mm_rope: the fused epilogue needs head_dim 128 (got %d); run the GEMM and b200_rope_neox", head_dim);
+  if (M == 0) return B200_OK;
+  const int arch = b200_sm_arch();
+  B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED,
+               "fp8_blockwise_scaled_mm_rope: requires an sm_100 device (got sm_%d); no fallback", arch);
+  B200_REQUIRE(skinny_applicable_fp8(M, N, K), B200_ERR_UNSUPPORTED,
+               "fp8_blockwise_scaled_mm_rope: M=%d N=%d K=%d belongs to the large-M kernel; run the GEMM and b200_rope_neox", M, N, K);
+  SkinnyParams sp{};
+  sp.sa = sa; sp.sa_sm = sa_sm; sp.sa_sk = sa_sk;
+  sp.sb = sb; sp.sb_sk = sb_sk; sp.sb_sn = sb_sn;
+  sp.bias = nullptr; sp.out = out; sp.ldo = ldo; sp.out_bf16 = out_dtype == B200_BF16;
+  sp.M = M; sp.N = N; sp.K = K;
+  sp.rope_cs = reinterpret_cast<const float2*>(cos_sin); sp.rope_cols = rope_cols;
+  return launch_skinny<0>(a, lda, b, ldb, sp, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
 namespace b200 {
 // dense half-precision GEMM out = A[M,K] . W[N,K]^T (+bias); used by the AWQ W4A16 linear
 int dense_half_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, const void* bias, void* out, int64_t ldo,

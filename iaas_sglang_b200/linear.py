@@ -33,10 +33,14 @@ class Fp8BlockLinearMethod:
         return out.to(dtype=x.dtype).view(*out_shape)
 
     def apply_quantized(self, layer, x_q: torch.Tensor, x_s: torch.Tensor, out_dtype: torch.dtype,
-                        bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+                        bias: Optional[torch.Tensor] = None, rope: Optional[tuple] = None) -> torch.Tensor:
         """The same linear when the producer of x already emitted its group-128 quantisation
-        (ops.rmsnorm_quant_fp8 / ops.silu_and_mul_quant_fp8): fp8_utils.py:205-207 without :202-204."""
-        out = ops.fp8_blockwise_scaled_mm(x_q, layer.weight.t(), x_s, layer.weight_scale_inv.t(), out_dtype)
+        (ops.rmsnorm_quant_fp8 / ops.silu_and_mul_quant_fp8): fp8_utils.py:205-207 without :202-204.
+        rope = (positions, rope_cols, head_dim, theta, cos_sin) for a qkv projection: the rotary embedding that follows it
+        (models/llama.py:186-188) runs in the GEMM's epilogue where it can (ops.fp8_blockwise_scaled_mm)."""
+        if bias is not None and rope is not None:
+            raise NotImplementedError("rope fusion with a bias (the bias would have to be added before the rotation)")
+        out = ops.fp8_blockwise_scaled_mm(x_q, layer.weight.t(), x_s, layer.weight_scale_inv.t(), out_dtype, rope=rope)
         return out if bias is None else out + bias
 
 

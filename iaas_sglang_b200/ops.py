@@ -51,11 +51,15 @@ def reserve_gemm_workspace(device, nbytes: int) -> None:
 # quantised GEMMs
 # ---------------------------------------------------------------------------------------------
 def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor, scales_b: torch.Tensor,
-                            out_dtype: torch.dtype) -> torch.Tensor:
+                            out_dtype: torch.dtype, *, rope: Optional[tuple] = None) -> torch.Tensor:
     """sgl_kernel.fp8_blockwise_scaled_mm (gemm.py:24-31; fp8_blockwise_gemm_kernel.cu:345-423).
 
     mat_a [M,K] e4m3 row-major; mat_b [K,N] e4m3 column-major; scales_a [M,K/128] f32 M-major;
-    scales_b [K/128,N/128] f32 K-major; returns [M,N] out_dtype.  Checks follow :351-383."""
+    scales_b [K/128,N/128] f32 K-major; returns [M,N] out_dtype.  Checks follow :351-383.
+    rope = (positions int64 [M], rope_cols, head_dim, theta, cos_sin): a qkv projection whose first rope_cols output
+    columns (q then k heads) get the neox rotary embedding (models/llama.py:186-188 qkv_proj -> rotary_emb) -- in the
+    GEMM's epilogue where the decode-shape kernel serves the shape (head_dim 128; cos_sin = rope_cos_sin(positions, ...),
+    computed once per step), otherwise (or with cos_sin None) by rope_neox_ on the result: the same bits."""
     dev = require_cuda(mat_a, mat_b, scales_a, scales_b)
     if mat_a.dim() != 2 or mat_b.dim() != 2:
         raise RuntimeError("mat_a and mat_b must be a matrix")
@@ -89,10 +93,49 @@ def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: 
     nbytes = lib.b200_gemm_workspace_size(M, N, K)
     ws = gemm_workspace(dev, nbytes)
     with torch.cuda.device(dev):
+        if rope is not None:
+            positions, rope_cols, head_dim, theta, cos_sin = rope
+            if positions.dtype != torch.int64 or not positions.is_contiguous() or positions.numel() != M or not positions.is_cuda:
+                raise RuntimeError("rope positions must be a contiguous int64 CUDA tensor with M entries")
+            if rope_cols % head_dim != 0 or not 0 <= rope_cols <= N:
+                raise RuntimeError("rope_cols must be a multiple of head_dim, at most N")
+            if cos_sin is not None:
+                if (cos_sin.dtype != torch.float32 or not cos_sin.is_contiguous() or not cos_sin.is_cuda
+                        or tuple(cos_sin.shape) != (M, head_dim // 2, 2)):
+                    raise RuntimeError("cos_sin must be a contiguous float32 CUDA tensor [M, head_dim / 2, 2] (ops.rope_cos_sin)")
+                rc = lib.b200_fp8_blockwise_scaled_mm_rope(
+                    ptr(mat_a), mat_a.stride(0), ptr(mat_b), mat_b.stride(1), ptr(scales_a), scales_a.stride(0),
+                    scales_a.stride(1), ptr(scales_b), scales_b.stride(0), scales_b.stride(1), ptr(out), out.stride(0),
+                    DTYPE_CODE[out_dtype], M, N, K, ptr(cos_sin), int(rope_cols), int(head_dim), ptr(ws), ws.numel(),
+                    current_stream(dev))
+                if rc != _lib.B200_ERR_UNSUPPORTED:
+                    check(rc)
+                    return out
         check(lib.b200_fp8_blockwise_scaled_mm(
             ptr(mat_a), mat_a.stride(0), ptr(mat_b), mat_b.stride(1), ptr(scales_a), scales_a.stride(0),
             scales_a.stride(1), ptr(scales_b), scales_b.stride(0), scales_b.stride(1), ptr(out), out.stride(0),
             DTYPE_CODE[out_dtype], M, N, K, ptr(ws), ws.numel(), current_stream(dev)))
+    if rope is not None:   # shape outside the fused epilogue: the same result from two launches
+        positions, rope_cols, head_dim, theta, _ = rope
+        if rope_cols > head_dim:   # (q heads and k heads are adjacent column blocks: any split of them gives the same bits)
+            rope_neox_(out[:, :rope_cols - head_dim], out[:, rope_cols - head_dim:rope_cols], positions, head_dim, theta)
+        elif rope_cols == head_dim:
+            rope_neox_(out[:, :head_dim], out[:, :0], positions, head_dim, theta)
+    return out
+
+
+def rope_cos_sin(positions: torch.Tensor, head_dim: int, theta: float = 10000.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[M, head_dim / 2, 2] float32 (cos, sin) rows of this step's positions -- rotary_embedding.py _compute_cos_sin_cache
+    indexed by `positions`, in the precision rope_neox_ evaluates them.  Once per decode step; every layer's qkv GEMM
+    rotates q and k with it in its epilogue (fp8_blockwise_scaled_mm(rope=...))."""
+    dev = require_cuda(positions)
+    if positions.dtype != torch.int64 or not positions.is_contiguous():
+        raise RuntimeError("positions must be a contiguous int64 tensor")
+    M = positions.numel()
+    if out is None:
+        out = torch.empty(M, head_dim // 2, 2, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(load().b200_rope_cos_sin(ptr(positions), M, int(head_dim), float(theta), ptr(out), current_stream(dev)))
     return out
 
 

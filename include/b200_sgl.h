@@ -283,6 +283,17 @@ int b200_fp8_blockwise_scaled_mm(const void* a, int64_t lda, const void* b, int6
                                  int64_t sa_stride_m, int64_t sa_stride_k, const float* sb, int64_t sb_stride_k,
                                  int64_t sb_stride_n, void* out, int64_t ldo, int out_dtype, int M, int N, int K,
                                  void* workspace, size_t workspace_bytes, void* stream);
+/* b200_fp8_blockwise_scaled_mm for a qkv projection followed by neox RoPE (python/sglang/srt/layers/rotary_embedding.py
+ * forward_native, is_neox_style; the call pair python/sglang/srt/models/llama.py:186-188 qkv_proj -> rotary_emb) in ONE
+ * launch: the first rope_cols output columns (q heads then k heads, head_dim columns each) are rotated with token m's row of
+ * cos_sin [M, head_dim / 2, 2] f32 (b200_rope_cos_sin below: once per decode step, the positions are the same for every
+ * layer); bit-identical to b200_fp8_blockwise_scaled_mm followed by b200_rope_neox on those columns.
+ * B200_ERR_UNSUPPORTED (run the two calls) unless head_dim == 128 and the decode-shape kernel serves (M, N, K). */
+int b200_fp8_blockwise_scaled_mm_rope(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
+                                      int64_t sa_stride_m, int64_t sa_stride_k, const float* sb, int64_t sb_stride_k,
+                                      int64_t sb_stride_n, void* out, int64_t ldo, int out_dtype, int M, int N, int K,
+                                      const float* cos_sin, int rope_cols, int head_dim, void* workspace,
+                                      size_t workspace_bytes, void* stream);
 /* int8_scaled_mm (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747; schema common_extension.cc:101-104):
  *   out[m,n] = ((float)(sum_k a[m,k]*b[k,n]) * sa[m]) * sb[n] + bias[n]
  * a: [M,K] int8 row-major; b: [K,N] column-major; bias: [N] of out dtype or NULL. */
@@ -327,6 +338,9 @@ int b200_silu_mul_quant_fp8(const void* x, void* q, int64_t q_stride_m, float* s
 int b200_silu_and_mul(const void* x, void* out, int dtype, int M, int d, void* stream);
 /* in-place neox-style rotary embedding on q [M,Hq,D] and k [M,Hkv,D] (heads contiguous, row strides in
  * elements: q and k may be column slices of one packed qkv tensor), positions int64 [M] */
+/* cos_sin[m][i] = (cos, sin)(positions[m] * theta^(-2 i / head_dim)), i < head_dim / 2 -- the rows of the reference's
+ * cos_sin_cache (rotary_embedding.py _compute_cos_sin_cache) for this step's positions, in f32 as b200_rope_neox evaluates them */
+int b200_rope_cos_sin(const int64_t* positions, int M, int head_dim, float theta, float* cos_sin, void* stream);
 int b200_rope_neox(void* q, int64_t q_stride_m, void* k, int64_t k_stride_m, const int64_t* positions, int dtype, int M,
                    int Hq, int Hkv, int D, float theta, void* stream);
 

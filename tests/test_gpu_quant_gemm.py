@@ -107,6 +107,34 @@ def test_fp8_large_m_kernel_split_k(M, N, K, split):
         _lib.tune_set("gb_split", old_s)
 
 
+@pytest.mark.parametrize("M,Hq,Hkv,K", [(64, 32, 8, 4096), (1, 32, 8, 4096), (37, 16, 4, 4096), (128, 24, 8, 4096),
+                                        (64, 8, 2, 512), (100, 10, 2, 5120), (256, 12, 2, 4096)])
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16], ids=["bf16", "f16"])
+def test_fp8_qkv_gemm_with_fused_rope_is_bit_identical_to_gemm_then_rope(M, Hq, Hkv, K, dt):
+    """qkv projection + neox RoPE in the GEMM's epilogue (decode-shape kernel, head_dim 128) against the GEMM followed by
+    ops.rope_neox_: the same bits on the q and k heads, v untouched; shapes the large-M kernel serves (M = 256) take the
+    two-launch path inside the same call."""
+    from iaas_sglang_b200 import ops
+
+    D = 128
+    N = (Hq + 2 * Hkv) * D
+    a, b, sa, sb = make_fp8_gemm_case(M, N, K, seed=M + N + K, dist="realistic")
+    g = torch.Generator().manual_seed(M)
+    pos = torch.randint(0, 131072, (M,), generator=g, dtype=torch.int64).cuda()
+    a, b, sa, sb = a.cuda(), _col_major(b), _col_major(sa), _col_major(sb)
+    want = ops.fp8_blockwise_scaled_mm(a, b, sa, sb, dt)
+    plain = want.clone()
+    ops.rope_neox_(want[:, :Hq * D], want[:, Hq * D:(Hq + Hkv) * D], pos, D, 500000.0)
+    cs = ops.rope_cos_sin(pos, D, 500000.0)
+    got = ops.fp8_blockwise_scaled_mm(a, b, sa, sb, dt, rope=(pos, (Hq + Hkv) * D, D, 500000.0, cs))
+    got2 = ops.fp8_blockwise_scaled_mm(a, b, sa, sb, dt, rope=(pos, (Hq + Hkv) * D, D, 500000.0, None))   # two launches
+    assert torch.equal(got2.view(torch.int16), want.view(torch.int16))
+    torch.cuda.synchronize()
+    assert torch.equal(got[:, (Hq + Hkv) * D:], plain[:, (Hq + Hkv) * D:])        # v: plain GEMM output
+    assert not torch.equal(got[:, :Hq * D], plain[:, :Hq * D]) or M == 0          # q was rotated
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+
+
 def test_fp8_blockwise_fp16_out_and_preconditions():
     from iaas_sglang_b200 import ops
 

@@ -441,10 +441,11 @@ __global__ void __launch_bounds__(AR_ROW_THREADS) allreduce_lamport_kernel(const
           if (lam_timed_out(t0, mine)) break;
         }
       } while (!all);
-      v[p.rank] = p.in[i];
+      // (no v[p.rank] = ...: a dynamically indexed array lives in local memory -- a stack frame in a latency-bound kernel)
+      const uint4 own = p.in[i];
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, v[q]);
+      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, q == p.rank ? own : v[q]);
       const uint4 o = lam_clean(pack8<BF16>(acc));
       if (p.mc) {
         multimem_st(reinterpret_cast<uint4*>(p.mc + buf_off) + red_off + i, o);
@@ -475,10 +476,11 @@ __global__ void __launch_bounds__(AR_ROW_THREADS) allreduce_lamport_kernel(const
           if (lam_timed_out(t0, mine)) break;
         }
       } while (!all);
-      v[p.rank] = p.in[i];
+      // (no v[p.rank] = ...: a dynamically indexed array lives in local memory -- a stack frame in a latency-bound kernel)
+      const uint4 own = p.in[i];
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, v[q]);
+      for (int q = 0; q < WORLD; ++q) add8<BF16>(acc, q == p.rank ? own : v[q]);
       return pack8<BF16>(acc);
     }
   };

@@ -135,8 +135,16 @@ __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" 
 // CTA c of `grid` owns the flattened tile range [c*W/grid, (c+1)*W/grid), W = NG * sum_b tiles(b): every SM
 // streams the same number of KV bytes whatever the length distribution, and there is one pipeline ramp-up per
 // SM per launch instead of one per (request, split) CTA.
-__device__ __forceinline__ int64_t part_start(int64_t c, int64_t W, int64_t grid) { return c * W / grid; }
-__device__ __forceinline__ int64_t part_owner(int64_t t, int64_t W, int64_t grid) { return ((t + 1) * grid - 1) / W; }
+// (32-bit division whenever W * grid fits: a 64-bit division is ~100 dependent instructions, and the merge kernel's warps
+// each do four of them before their first load)
+__device__ __forceinline__ int64_t part_start(int64_t c, int64_t W, int64_t grid) {
+  if ((((uint64_t)W * (uint64_t)grid) >> 32) == 0) return (int64_t)(((uint32_t)c * (uint32_t)W) / (uint32_t)grid);
+  return c * W / grid;
+}
+__device__ __forceinline__ int64_t part_owner(int64_t t, int64_t W, int64_t grid) {
+  if ((((uint64_t)W * (uint64_t)grid) >> 32) == 0) return (int64_t)((((uint32_t)t + 1u) * (uint32_t)grid - 1u) / (uint32_t)W);
+  return ((t + 1) * grid - 1) / W;
+}
 
 struct SegCursor {
   // walks the (b, g, tile) space from flattened tile t; tables live in shared memory

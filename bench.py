@@ -185,6 +185,7 @@ class StackBase:
 
         self.hidden_in = torch.zeros(batch, hidden, dtype=self.dtype, device=dev)
         self.positions = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.rope_cs = None   # per-step rotary cos / sin rows (forward() fills it; None = RoPE as its own launch, same bits)
         self.seq_lens = torch.ones(batch, dtype=torch.int64, device=dev)
         self.req_pool_indices = torch.zeros(batch, dtype=torch.int64, device=dev)
         self.out_cache_loc = torch.zeros(batch, dtype=torch.int64, device=dev)

@@ -10,7 +10,9 @@ pytestmark = pytest.mark.gpu
 TOL = 2e-3
 # MLA only: the reference's CPU kernel rounds every softmax weight to bf16 before P.V (decode.cpp:1157-1159), which
 # puts its OWN output ~2e-3 (relative L2, randn inputs) away from the exact softmax.  The CUDA kernel is held to
-# 2e-3 against the exact form (fp32 weights) and to 2x that against the reference's literally-rounded output.
+# 2e-3 against the exact form (fp32 weights) and to 2x that against the reference's literally-rounded output -- inside
+# the bar the reference's own MLA kernel test grants (sgl-kernel/tests/test_cutlass_mla.py:99: atol = rtol = 1e-2), which
+# tests/test_gpu_mla_boundary.py applies verbatim to the cutlass_mla_decode surface.
 TOL_MLA_LITERAL = 4e-3
 
 

@@ -224,6 +224,13 @@ def bench_proftp8():
     attn_case("cfg2tp8", 512, 4, 1, 128, 4096)
 
 
+def bench_proftp24():
+    """a few plain launches of the TP2- / TP4-local attention shapes of cfg 2 for ncu (-k regex:decode_attn_mma)"""
+    _plain_timeit()
+    attn_case("cfg2tp2", 128, 16, 4, 128, 4096)
+    attn_case("cfg2tp4", 256, 8, 2, 128, 4096)
+
+
 def bench_profgemm():
     """a few plain launches of decode-shape GEMMs for ncu (-k regex:gemm_skinny)"""
     global timeit

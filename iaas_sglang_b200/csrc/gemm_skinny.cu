@@ -604,19 +604,23 @@ bool skinny_applicable(int M) { return M <= 256; }
 // FP8 block-scaled: skinny (swap-AB, cluster split-K) or the persistent large-M kernel?  Measured policy
 // (tools/kb_cross.py over the TP-local shapes of cfg 2/4/5 at M 32 / 64 / 128, profiles/r02_kb_cross.txt, second table:
 // after the write-out of this kernel lost its GPU-scope fences and its divisions): the large-M kernel wins at every
-// M > 128, on short K loops (K <= 2304; K <= 1024 at M <= 32), on the widest weights at K <= 4096 (gate_up: 224 tiles
-// of 128 columns stream better from the persistent kernel) and, at 64 < M <= 128, wherever K <= 4096 meets N >= 6144 or
-// K < 4096; the skinny kernel wins everywhere else -- its split-K puts every SM to work on few-tile shapes.
+// M > 128, on short K loops (K <= 2304 from M = 49; K < 2048 from M = 33; K <= 1024 from M = 17), on the widest weights at
+// K <= 4096 from M = 49 (gate_up: 224 tiles of 128 columns stream better from the persistent kernel) and, at
+// 64 < M <= 128, below K = 3584 or where K = 3584 meets N > 4096; the skinny kernel wins everywhere else -- its split-K
+// puts every SM to work on few-tile shapes (third table of r02b_kb_cross.txt: M 16 / 48 / 96 / 128).
 // Knob sk_max_m >= 0 forces "skinny iff M <= sk_max_m".
 bool skinny_applicable_fp8(int M, int N, int K) {
   const int max_m = tune(TUNE_SK_MAX_M);
   if (max_m >= 0) return M <= (max_m > 256 ? 256 : max_m);
   if (M > 128) return false;
+  if (M <= 16) return true;
   if (M <= 32) return K >= 1536;
+  if (M <= 48) return K >= 2048;                       // (gate_up too: 28672 x 4096 at M = 48 23.8 us against 26.7)
   if (K <= 2304) return false;
   if (M <= 64) return !(K <= 4096 && N >= 16384);
-  if (K >= 7168) return true;
-  return K >= 4096 && N <= 4096;
+  if (K >= 7168) return true;                          // 64 < M <= 128 from here
+  if (K >= 4096) return N < 16384;
+  return K >= 3584 && N <= 4096;
 }
 
 struct SkinnyPlan {
@@ -685,7 +689,10 @@ static int launch_skinny_t(const CUtensorMap& tw, const CUtensorMap& tx, SkinnyP
     const bool fits = (P + (s2 - 1) * slice) * SK_BN * 4 <= ring_bytes;
     // (capacity + 1/15: the occupancy API under-counts clusters of 8 -- 32 tiles x 8 = 256 CTAs against an answer of 240
     // run in one wave, 14.1 us against 16.0 for S = 6 on 4096 x 14336; 48 x 6 = 288 against 264 do not: 14.2 against 9.7 for S = 5)
-    if (sp.n_tiles * s2 <= capacity[s2] + capacity[s2] / 15 && sp.kb_total / s2 >= 2 && fits && sp.n_tiles * s2 > best) {
+    // (only the two-CTAs-per-SM variants: at M > 64 the API's answer is exact -- 48 x 3 = 144 CTAs against 138 ran in two
+    // waves, 19.5 us instead of 13.1)
+    const int cap2 = capacity[s2] + ((COLS * GROUPS <= 64) ? capacity[s2] / 15 : 0);
+    if (sp.n_tiles * s2 <= cap2 && sp.kb_total / s2 >= 2 && fits && sp.n_tiles * s2 > best) {
       S = s2;
       best = sp.n_tiles * s2;
     }

@@ -36,7 +36,7 @@ def case(M, N, K):
         ops.fp8_blockwise_scaled_mm(a, ws_[i].t(), sa, sb, torch.bfloat16)
 
     out = {}
-    for name, max_m in (("skinny", 256), ("large", 0)):
+    for name, max_m in (("skinny", 256), ("large", 0), ("policy", -1)):
         _lib.tune_set("sk_max_m", max_m)
         out[name] = kbench.timeit(run, nv) * 1e3
     return out
@@ -51,8 +51,10 @@ def main():
                 r = case(m, n, k)
                 floor = (n * k + m * k + m * n * 2) / kbench.HBM / 1e3
                 win = "skinny" if r["skinny"] <= r["large"] else "large"
+                best = min(r["skinny"], r["large"])
+                flag = "  <-- policy off by %.0f%%" % (100 * (r["policy"] / best - 1)) if r["policy"] > 1.06 * best else ""
                 print(f"{grp:9s} N{n:6d} K{k:6d} M{m:4d}  skinny {r['skinny']:7.1f} us  large {r['large']:7.1f} us  "
-                      f"hbm floor {floor:6.1f} us  -> {win}", flush=True)
+                      f"policy {r['policy']:7.1f} us  hbm floor {floor:6.1f} us  -> {win}{flag}", flush=True)
                 rows.append(dict(group=grp, N=n, K=k, M=m, skinny_us=round(r["skinny"], 2), large_us=round(r["large"], 2),
                                  hbm_floor_us=round(floor, 2)))
     _lib.tune_set("sk_max_m", old)

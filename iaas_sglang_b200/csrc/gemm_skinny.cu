@@ -623,6 +623,20 @@ bool skinny_applicable_fp8(int M, int N, int K) {
   return K >= 3584 && N <= 4096;
 }
 
+// INT8 (per-token / per-channel scales, exact int32 accumulation in TMEM over the whole K range: no per-k-block promotion,
+// so the large-M kernel has less to lose than in FP8): measured crossover in tools/kb_cross.py --int8.
+bool skinny_applicable_int8(int M, int N, int K) {
+  const int max_m = tune(TUNE_SK_MAX_M);
+  if (max_m >= 0) return M <= (max_m > 256 ? 256 : max_m);
+  // profiles/r02b_kb_cross_int8.txt: the decode-shape kernel wins at every M <= 128 except the widest weight at K <= 4096
+  // (28672 x 4096 at M = 128: 31.3 us against 28.4), and at M = 129 .. 256 on long K or few tiles (4096 x 14336: 27 against
+  // 42; 1280 x 8192: 19.5 against 27.7); the large-M kernel takes the rest (4096 x 1024 at M = 256: 12.3 against 16.7)
+  if (M > 256) return false;   // (the decode-shape kernel's limit)
+  if (M <= 64) return true;
+  if (M <= 128) return !(K <= 4096 && N >= 16384);
+  return K >= 7168 || (K >= 4096 && N <= 4096);
+}
+
 struct SkinnyPlan {
   int stages, tab_cap, smem;
 };

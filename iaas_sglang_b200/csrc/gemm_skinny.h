@@ -32,6 +32,7 @@ struct SkinnyParams {
 
 size_t skinny_workspace_bytes(int M, int N, int K);
 bool skinny_applicable(int M);      // int8 / AWQ decode shapes and workspace sizing
+bool skinny_applicable_int8(int M, int N, int K); // int8: measured policy
 bool skinny_applicable_fp8(int M, int N, int K);  // fp8 block-scaled: measured policy skinny vs large-M kernel
 // a [M,K] activations, w [N,K] weight (both K-major, 1-byte elements); MODE 0 fp8 block-scaled, 1 int8;
 // MODE 2: a = half activations [M,K] (lda in BYTES), w = AWQ qweight int32 [K, N/8] (ldw in BYTES)

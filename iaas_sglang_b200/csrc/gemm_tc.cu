@@ -447,7 +447,7 @@ extern "C" int b200_int8_scaled_mm(const void* a, int64_t lda, const void* b, in
   if (M == 0) return B200_OK;
   const int arch = b200_sm_arch();
   B200_REQUIRE(arch >= 100 && arch < 110, B200_ERR_UNSUPPORTED, "int8_scaled_mm: requires an sm_100 device (got sm_%d); no fallback", arch);
-  if (skinny_applicable(M)) {
+  if (skinny_applicable_int8(M, N, K)) {
     SkinnyParams sp{};
     sp.sa = sa; sp.sb = sb; sp.bias = bias; sp.out = out; sp.ldo = ldo; sp.out_bf16 = out_dtype == B200_BF16;
     sp.M = M; sp.N = N; sp.K = K;

@@ -8,7 +8,8 @@ import json
 import os
 import sys
 
-ms_list = [int(a) for a in sys.argv[1:]] or [32, 64, 96, 128, 160, 192, 256]
+INT8 = "--int8" in sys.argv
+ms_list = [int(a) for a in sys.argv[1:] if a != "--int8"] or [32, 64, 96, 128, 160, 192, 256]
 sys.argv = sys.argv[:1]
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import kbench  # noqa: E402
@@ -22,6 +23,24 @@ SHAPES = {
     "cfg4 tp8": [(1280, 8192), (8192, 1024), (7168, 8192), (8192, 3584)],
     "cfg5 tp8": [(2112, 7168), (3072, 1536), (7168, 2048), (4608, 7168), (7168, 2304)],
 }
+
+
+def case_int8(M, N, K):
+    g = torch.Generator(device=kbench.DEV).manual_seed(0)
+    nv = max(1, min(16, kbench.L2_BYTES // (N * K) + 1))
+    ws_ = [torch.randint(-127, 128, (N, K), device=kbench.DEV, generator=g, dtype=torch.int8) for _ in range(nv)]
+    a = torch.randint(-127, 128, (M, K), device=kbench.DEV, generator=g, dtype=torch.int8)
+    sa = torch.rand(M, device=kbench.DEV, generator=g) * 1e-3
+    sb = torch.rand(N, device=kbench.DEV, generator=g) * 1e-3
+
+    def run(i):
+        ops.int8_scaled_mm(a, ws_[i].t(), sa, sb, torch.bfloat16, None)
+
+    out = {}
+    for name, max_m in (("skinny", 256), ("large", 0), ("policy", -1)):
+        _lib.tune_set("sk_max_m", max_m)
+        out[name] = kbench.timeit(run, nv) * 1e3
+    return out
 
 
 def case(M, N, K):
@@ -48,7 +67,7 @@ def main():
     for grp, shapes in SHAPES.items():
         for n, k in shapes:
             for m in ms_list:
-                r = case(m, n, k)
+                r = case_int8(m, n, k) if INT8 else case(m, n, k)
                 floor = (n * k + m * k + m * n * 2) / kbench.HBM / 1e3
                 win = "skinny" if r["skinny"] <= r["large"] else "large"
                 best = min(r["skinny"], r["large"])

@@ -213,6 +213,28 @@ def test_int8_scaled_mm_bit_exact(M, N, K, with_bias):
     assert torch.equal(out.cpu(), ref), max_abs(out, ref)
 
 
+@pytest.mark.parametrize("M,N,K", [(130, 1536, 4096), (200, 4096, 1024), (256, 1280, 8192), (256, 3072, 1536), (96, 4096, 512)])
+def test_int8_scaled_mm_both_kernels_bit_exact(M, N, K):
+    """Either side of the measured int8 policy (knob sk_max_m): the decode-shape kernel up to M = 256 and the large-M kernel
+    from M = 1 both equal the oracle bit for bit, so the policy can move without changing a result."""
+    from iaas_sglang_b200 import _lib, ops
+
+    g = torch.Generator().manual_seed(M + N + K)
+    a = (torch.randn(M, K, generator=g) * 5).clamp(-128, 127).round().to(torch.int8)
+    w = (torch.randn(N, K, generator=g) * 5).clamp(-128, 127).round().to(torch.int8)
+    sa, sb = torch.randn(M, generator=g), torch.randn(N, generator=g)
+    bias = (torch.randn(N, generator=g) * 10).to(torch.bfloat16)
+    ref = orc.int8_scaled_mm(a, w.t(), sa, sb, torch.bfloat16, bias)
+    old = _lib.tune_get("sk_max_m")
+    try:
+        for kernel, max_m in (("skinny", 256), ("large", 0), ("policy", old)):
+            _lib.tune_set("sk_max_m", max_m)
+            out = ops.int8_scaled_mm(a.cuda(), w.cuda().t(), sa.cuda(), sb.cuda(), torch.bfloat16, bias.cuda())
+            assert torch.equal(out.cpu(), ref), (kernel, max_abs(out, ref))
+    finally:
+        _lib.tune_set("sk_max_m", old)
+
+
 def test_int8_against_reference_golden_and_extremes():
     from iaas_sglang_b200 import ops
 

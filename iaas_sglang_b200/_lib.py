@@ -157,7 +157,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.b200_abi_version() != 3:
+    if lib.b200_abi_version() != 4:
         raise ImportError("libb200sgl.so ABI version mismatch")
     _lib = lib
     return lib

@@ -40,7 +40,9 @@ extern "C" {
 #define B200_F16 1
 #define B200_F32 2
 
-#define B200_SGL_ABI_VERSION 3
+/* 4: b200_ar_region_bytes grew (push-protocol receive buffers: regions sized by an older library are too small);
+ *    new entry points b200_decode_attn_static, b200_rope_cos_sin, b200_fp8_blockwise_scaled_mm_rope (no struct changed) */
+#define B200_SGL_ABI_VERSION 4
 #define B200_KV_E4M3 3   /* b200_decode_attn_params.kv_dtype */
 
 const char* b200_last_error(void);

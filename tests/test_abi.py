@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     raw = ctypes.CDLL(_lib.SO_PATH)
     for s in declared_symbols():
         assert hasattr(raw, s), s
-    assert lib.b200_abi_version() == 3
+    assert lib.b200_abi_version() == 4
 
 
 def test_struct_layout_matches_header():

@@ -715,7 +715,10 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
                                                                 const float* __restrict__ casc_lse,
                                                                 const float* __restrict__ pre_o,
                                                                 const float* __restrict__ pre_lse) {
-  griddep_wait();
+  // Everything up to the first read of a partial depends only on seq_lens (and the cascade prefix length), which the
+  // attention kernel does not write: it runs BEFORE the grid-dependency wait, i.e. under the tail of the attention kernel
+  // on the SMs its first finished CTAs have left.  (This kernel is a pure latency chain -- measured in place: 8.4 us after a
+  // 174 us attention kernel at cfg 2, 10.3 us at cfg 4 TP8 -- so every round trip taken off it counts.)
   griddep_launch();
   const int lane = threadIdx.x & 31;
   const int hblocks = (Hq + 7) >> 3;
@@ -723,11 +726,13 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   if (h >= Hq) return;
   const int64_t kv_start = kv_start_p ? (int64_t)*kv_start_p : 0;
   const bool cascade = casc_o != nullptr;
+  const bool tile_pow2 = (tile_t & (tile_t - 1)) == 0;
+  const int tile_sh = __ffs(tile_t) - 1;
   int all = 0, before = 0, tiles_b = 0;
   for (int i = lane; i < B; i += 32) {
     int64_t len = meta_at(seq_lens, i, lens32) - kv_start;
     if (len < 0) len = 0;
-    const int tl = (int)((len + tile_t - 1) / tile_t);
+    const int tl = tile_pow2 ? (int)((len + tile_t - 1) >> tile_sh) : (int)((len + tile_t - 1) / tile_t);   // (no 64-bit division)
     all += tl;
     if (i < b) before += tl;
     if (i == b) tiles_b = tl;
@@ -740,6 +745,7 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   }
   uint16_t* orow = out + ((int64_t)b * Hq + h) * Dv;
   if (tiles_b == 0 && !cascade) {  // seq_len == 0: defined output (zeros)
+    griddep_wait();
     for (int d = lane; d < Dv; d += 32) orow[d] = 0;
     if constexpr (QUANT) merge_quant_row<BF16>(mq, make_uint2(0u, 0u), b, h, lane);
     return;
@@ -751,6 +757,7 @@ __global__ void __launch_bounds__(256) decode_merge_part_kernel(const float* __r
   const int64_t t0 = (int64_t)NG * before + (int64_t)g * tiles_b, t1 = t0 + tiles_b;
   const int c0 = tiles_b > 0 ? (int)part_owner(t0, W, grid) : 0, c1 = tiles_b > 0 ? (int)part_owner(t1 - 1, W, grid) : 0;
   const bool whole = c0 == c1;  // one CTA saw the whole unit
+  griddep_wait();               // from here on: what the attention kernel wrote
   if (whole && !cascade) {      // ... and wrote the output itself
     if constexpr (QUANT) merge_quant_row<BF16>(mq, *reinterpret_cast<const uint2*>(orow + lane * 4), b, h, lane);
     return;
